@@ -1,0 +1,78 @@
+// Shared context / workspace / error plumbing for the corsair_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/corsair_b200.h"
+
+struct cb_ctx {
+    int device = 0;
+    int sm_count = 148;
+    char* arena = nullptr;      // device workspace
+    size_t arena_bytes = 0;
+    size_t arena_off = 0;       // bump pointer, reset at the start of every public call
+    int64_t launches = 0;
+    int knn_variant = 0;        // 0 auto, 1 simt, 2 tcgen05
+    char err[512] = {0};
+};
+
+#define CB_FAIL(ctx, code, ...)                                  \
+    do {                                                         \
+        snprintf((ctx)->err, sizeof((ctx)->err), __VA_ARGS__);   \
+        return (code);                                           \
+    } while (0)
+
+#define CB_CUDA(ctx, expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t e_ = (expr);                                                             \
+        if (e_ != cudaSuccess)                                                               \
+            CB_FAIL(ctx, CB_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_),   \
+                    __FILE__, __LINE__);                                                     \
+    } while (0)
+
+#define CB_LAUNCH_CHECK(ctx)                                                                 \
+    do {                                                                                     \
+        (ctx)->launches++;                                                                   \
+        cudaError_t e_ = cudaGetLastError();                                                 \
+        if (e_ != cudaSuccess)                                                               \
+            CB_FAIL(ctx, CB_ECUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), \
+                    __FILE__, __LINE__);                                                     \
+    } while (0)
+
+// Start of a public call: select the device and rewind the arena.
+int cb_begin(cb_ctx* ctx);
+// Bump-allocate `bytes` (256-byte aligned) from the arena; grows the arena (synchronising the
+// device) when it is too small.  Returns nullptr and sets ctx->err on failure.
+void* cb_alloc(cb_ctx* ctx, size_t bytes);
+// Make sure the arena holds at least `bytes` in total BEFORE any cb_alloc of this call (growing
+// in the middle of a call would invalidate earlier sub-allocations).
+int cb_reserve(cb_ctx* ctx, size_t bytes);
+
+static inline size_t cb_align(size_t b) { return (b + 255) & ~size_t(255); }
+
+template <typename T>
+static inline T* cb_alloc_t(cb_ctx* ctx, size_t n) {
+    return reinterpret_cast<T*>(cb_alloc(ctx, n * sizeof(T)));
+}
+
+static inline int cb_div_up(int a, int b) { return (a + b - 1) / b; }
+
+// ---- device helpers ---------------------------------------------------------------------
+__device__ __forceinline__ uint64_t cb_splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+// minimal-set draw shared by the fit kernel and cb_draw_minimal_sets (see the header)
+__device__ __forceinline__ int cb_draw_index(uint64_t seed, uint64_t counter, int m) {
+    uint64_t x = cb_splitmix64(seed * 0x9E3779B97F4A7C15ull + counter);
+    return (int)(((x >> 32) * (uint64_t)(uint32_t)m) >> 32);
+}
+
+// internal entry points shared between translation units
+int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k,
+                int metric, int64_t* idx, float* dist, int32_t* idx32, cudaStream_t st);

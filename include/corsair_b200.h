@@ -1,0 +1,183 @@
+/* corsair_b200 -- C ABI of the B200-native correspondence-and-registration hot path.
+ *
+ * The reference (ExistentialRobotics/CORSAIR) has no FFI of its own: its boundary for this
+ * path is a set of plain Python functions (utils/find_nn.py, utils/eval_pose.py,
+ * utils/symmetry.py, utils/preprocess.py, utils/retrieval.py, utils/pc_dist.py,
+ * utils/_transform_estimation.py).  Each entry point below names the reference function(s)
+ * (file:line under the reference tree) whose arithmetic it replaces; the Python modules in
+ * corsair_b200/ keep the reference signatures and call these through ctypes.
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer owned by the caller, unless the parameter name
+ *     starts with h_ (host).  The library never frees or retains caller memory.
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy
+ *     default stream) and never synchronises, unless documented otherwise.
+ *   - a cb_ctx owns a device workspace arena; one ctx serves one stream at a time.
+ *   - return value: 0 on success, negative cb_status otherwise; text via cb_last_error().
+ *   - matrices are row-major; poses are row-major 4x4.
+ */
+#ifndef CORSAIR_B200_H
+#define CORSAIR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cb_ctx cb_ctx;
+
+enum cb_status {
+    CB_OK = 0,
+    CB_EINVAL = -1,       /* bad argument (shape, null pointer, unsupported k ...) */
+    CB_ECUDA = -2,        /* CUDA runtime error (message holds cudaGetErrorString) */
+    CB_ENOMEM = -3,       /* workspace allocation failed */
+    CB_EUNSUPPORTED = -4, /* valid request the kernels do not cover (e.g. feature width) */
+    CB_ENCCL = -5
+};
+
+/* metric selectors */
+enum cb_knn_metric {
+    CB_KNN_SQL2 = 0,   /* squared L2, "SquareL2" of utils/find_nn.py:28-29 */
+    CB_KNN_L2 = 1,     /* sqrt(d2 + 1e-7), "L2" of utils/find_nn.py:25-27 */
+    CB_KNN_MAXDOT = 2  /* largest inner product, utils/_transform_estimation.py:149-150 */
+};
+enum cb_retrieval_metric {
+    CB_RET_EUCLID = 0, /* scipy cdist default, utils/retrieval.py:175 */
+    CB_RET_COSINE = 1  /* scipy pdist "cosine", utils/retrieval.py:24,84,131 */
+};
+
+int cb_version(void);
+int cb_create(cb_ctx** out, int device, size_t workspace_bytes);
+int cb_destroy(cb_ctx* ctx);
+const char* cb_last_error(const cb_ctx* ctx);
+/* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
+int64_t cb_launch_count(const cb_ctx* ctx);
+/* name of the kNN candidate kernel variant the ctx dispatches to: "tcgen05" or "simt" */
+const char* cb_knn_variant(const cb_ctx* ctx);
+/* force a kNN candidate variant (0 = auto, 1 = simt fp32, 2 = tcgen05 bf16x3); for tests/bench */
+int cb_set_knn_variant(cb_ctx* ctx, int variant);
+
+/* ---- K1: feature-space kNN -------------------------------------------------------------
+ * Replaces find_nn_cpu / find_knn_cpu (utils/find_nn.py:34-49, scipy KDTree in float64, the
+ * kNN the shipped pipeline runs at utils/eval_pose.py:68,71) and find_nn_gpu / find_knn_gpu
+ * (utils/find_nn.py:52-119, broadcast pdist + min/topk).
+ * q [nq,d], r [nr,d] float32.  idx [nq,k] int64, dist [nq,k] float32 (may be NULL), rows
+ * sorted ascending by (exact float64 difference-form distance, index).  For CB_KNN_MAXDOT the
+ * order is descending inner product and dist holds the products.
+ * mutual (may be NULL) [nq] uint8: 1 iff the query is also the nearest reference's nearest
+ * query (k-th column 0 only; new, not in the reference).
+ * 1 <= k <= 64, k <= nr, 1 <= d <= 256. */
+int cb_knn(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k, int metric,
+           int64_t* idx, float* dist, uint8_t* mutual, void* stream);
+
+/* Ragged batch of independent kNN problems sharing d,k,metric: problem p uses query rows
+ * [h_q_off[p], h_q_off[p+1]) of q and reference rows [h_r_off[p], h_r_off[p+1]) of r; idx
+ * holds indices LOCAL to the problem's reference block.  Replaces the per-segment loop of
+ * split_corr (utils/symmetry.py:145-179).  h_q_off/h_r_off are HOST arrays of n_problems+1. */
+int cb_knn_ragged(cb_ctx* ctx, const float* q, const float* r, int d, int k, int metric,
+                  const int32_t* h_q_off, const int32_t* h_r_off, int n_problems, int64_t* idx,
+                  float* dist, void* stream);
+
+/* Dense pairwise distance tile, pdist (utils/find_nn.py:24-31): out [n,m] float32,
+ * dist_type 0 = SquareL2, 1 = L2 (+1e-7 under the root). */
+int cb_pdist(cb_ctx* ctx, const float* a, int n, const float* b, int m, int d, int dist_type,
+             float* out, void* stream);
+
+/* Dense inner-product matrix F0 F1^T (utils/_transform_estimation.py:149, return_corr=True). */
+int cb_dot_matrix(cb_ctx* ctx, const float* a, int n, const float* b, int m, int d, float* out,
+                  void* stream);
+
+/* ---- K2: global-descriptor retrieval ----------------------------------------------------
+ * Replaces scipy cdist + np.argsort (utils/retrieval.py:139-141,175; evaluation-scan2cad.py
+ * :322-323) and cosine pdist + argsort of get_rank / retrieval_eval (utils/retrieval.py:84,
+ * 129-136).  q [nq,d], db [ndb,d] float32.  For each query the k best database rows in
+ * ascending (float64 distance, index) order: idx [nq,k] int32, dist [nq,k] float64 (may be
+ * NULL; Euclidean distance, not squared, or cosine distance).  exclude_self != 0 drops column
+ * j == query row + self_offset (get_rank's positional self-exclusion).  1 <= k <= ndb. */
+int cb_retrieval_topk(cb_ctx* ctx, const float* q, int nq, const float* db, int ndb, int d, int k,
+                      int metric, int exclude_self, int self_offset, int32_t* idx, double* dist,
+                      void* stream);
+
+/* ---- K3: correspondence RANSAC ----------------------------------------------------------
+ * Replaces registration_based_on_corr (utils/eval_pose.py:82-100), i.e. Open3D's
+ * registration_ransac_based_on_correspondence(ransac_n=10, point-to-point, no scaling,
+ * max_iteration 100000, confidence 0.999) on an identity correspondence set.
+ * src_xyz [n_src,3], tgt_xyz [n_tgt,3] float32; correspondence i pairs
+ * src_xyz[src_idx[i]] with tgt_xyz[tgt_idx[i]] (int64 index arrays of length m; either may be
+ * NULL = identity).  Hypothesis h fits minimal set h: minimal [h_total, ransac_n] int32 if
+ * given, else drawn on device by cb_draw_minimal_sets' counter-based rule from `seed`.
+ * adaptive != 0 applies Open3D's early-termination rule in hypothesis order.
+ * Outputs (device): T [16] float64, stats [4] float64 = {best_h, inliers, sum_d2,
+ * n_evaluated}; counts [h_total] int32 and sums [h_total] float64 (may be NULL) receive the
+ * per-hypothesis inlier count / sum of squared inlier distances for h < n_evaluated waves. */
+int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const float* tgt_xyz, int n_tgt,
+              const int64_t* src_idx, const int64_t* tgt_idx, int m, const int32_t* minimal,
+              uint64_t seed, int h_total, int ransac_n, double max_dist, int adaptive,
+              double confidence, double* T, double* stats, int32_t* counts, double* sums,
+              void* stream);
+
+/* The library's seeded minimal-set rule, exported so the oracle consumes identical sets:
+ * set[h][j] = (hi32(splitmix64(seed*0x9E3779B97F4A7C15 + h*ransac_n + j)) * m) >> 32.
+ * out [h_total, ransac_n] int32 (device). */
+int cb_draw_minimal_sets(cb_ctx* ctx, uint64_t seed, int m, int h_total, int ransac_n,
+                         int32_t* out, void* stream);
+
+/* Batched Umeyama fits only (Open3D TransformationEstimationPointToPoint, a10 in SURVEY §8):
+ * T_all [h_total,16] float64. */
+int cb_fit_minimal(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, int m,
+                   const int32_t* minimal, int h_total, int ransac_n, double* T_all, void* stream);
+
+/* ---- K4: Chamfer ------------------------------------------------------------------------
+ * One-direction: mean over a of the Euclidean distance to the nearest b, after a <- T a
+ * (T [16] float64 row-major 4x4, may be NULL): chamfer_kdtree_1direction(apply_transform(..))
+ * (utils/preprocess.py:39-48,67-70) and chamfer_gpu_1direction (:59-64).
+ * two_dir != 0 adds the reverse direction: chamfer_gpu (:51-56) == pc_dist.chamfer
+ * (utils/pc_dist.py:45-52).  a [na,3], b [nb,3] float32; out [1] float64 (device).
+ * nn_idx (may be NULL) [na] int32 receives the nearest-b index of each a. */
+int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
+               int two_dir, double* out, int32_t* nn_idx, void* stream);
+
+/* All-pairs two-direction Chamfer rows of compute_dist (utils/pc_dist.py:61-99):
+ * pts [L,P,3] float32; out [(row1-row0), L] float64 rows row0..row1-1 of the full symmetric
+ * table with diagonal 100. */
+int cb_chamfer_matrix(cb_ctx* ctx, const float* pts, int L, int P, int row0, int row1, double* out,
+                      void* stream);
+
+/* Hausdorff-style max of NN distances (evaluation-shapenet.py:122-155 chamfer_max), same
+ * arguments as cb_chamfer one-direction; out [1] float64. */
+int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
+              double* out, void* stream);
+
+/* ---- K3': symmetric_cut4 pieces (utils/symmetry.py:182-259) -------------------------------
+ * feature rows + 50-NN (:201-214): for each of n_samples rows sample_idx[s] of feat [n,d], the
+ * n_nn nearest rows (itself included) as ASCENDING row indices: nn_idx [n_samples,n_nn] int32. */
+int cb_feature_rows_topk(cb_ctx* ctx, const float* feat, int n, int d, const int32_t* sample_idx,
+                         int n_samples, int n_nn, int32_t* nn_idx, void* stream);
+
+/* Batched tiny k-means (sklearn KMeans(n_clusters=K, random_state=0, n_init=10) on the n_nn
+ * gathered xyz, :216) + the acceptance statistics of :218-236.  rng_first [n_init] int32 and
+ * rng_unif [n_init,K-1,n_trials] float64 are the data-independent draws of sklearn's
+ * k-means++ (generated by the host shim from numpy RandomState).  Outputs per sample:
+ * centers [n_samples,K,3] float32, stats [n_samples,4] float32 = {min centre distance, max
+ * mean intra-cluster error, std of label ratios over all n points, inertia}. */
+int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx, int n_samples,
+                    int n_nn, int K, const int32_t* rng_first, const double* rng_unif, int n_init,
+                    int n_trials, float* centers, float* stats, void* stream);
+
+/* KMeans.predict over all n points (:224,:240): labels [n] int32 nearest of K centres
+ * (centers [K,3] float32), counts [K] int32 histogram (may be NULL). */
+int cb_assign_labels(cb_ctx* ctx, const float* xyz, int n, const float* centers, int K,
+                     int32_t* labels, int32_t* counts, void* stream);
+
+/* ---- K5: IRLS pose (utils/_transform_estimation.py:110-137) ------------------------------
+ * est_quad_linear_robust: iters (reference: 20) iterations of the linearised weighted solve.
+ * p0,p1 [n,3] float32, w [n] float32 (NULL = ones); T [16] float32 (device). */
+int cb_irls_pose(cb_ctx* ctx, const float* p0, const float* p1, const float* w, int n, int iters,
+                 float* T, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CORSAIR_B200_H */
