@@ -1,0 +1,420 @@
+// K1: feature-space kNN  (replaces utils/find_nn.py:34-119 of the reference).
+//
+// Engine E1 (d <= 32, k <= 12): approximate candidate pass + exact re-rank.
+//   1. row norms |r|^2 of the references (fp32) and their maximum
+//   2. candidate kernel: GEMM-form score s = |r|^2 - 2 q.r (or -q.r) per (query, ref chunk),
+//      keeps the KC best per chunk in registers.  Two variants: SIMT fp32 (this file) and
+//      tcgen05 split-bf16 tensor-core tiles (knn_tc.cu).
+//   3. re-rank: one warp per query recomputes the S*KC candidates in float64 difference form
+//      (unfused, sequential over the feature axis: bit-identical to the oracle), orders them by
+//      (distance, index) and PROVES that no dropped reference can belong to the top-k using the
+//      score error bound; rows that cannot be proven are queued
+//   4. fallback: queued rows are solved by exact float64 brute force.
+// Engine E2 (anything else): exact float64 distance rows + per-row radix select (select.cu).
+#include "common.cuh"
+#include "knn_internal.cuh"
+
+#include <float.h>
+#include <math.h>
+
+// ------------------------------------------------------------------------------- norms
+__global__ void knn_norms_kernel(const float* __restrict__ r, int nr, int d, float* __restrict__ rn,
+                                 unsigned int* __restrict__ rmax_bits) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    float s = 0.f;
+    if (j < nr) {
+        const float* p = r + (size_t)j * d;
+        for (int c = 0; c < d; ++c) s = fmaf(p[c], p[c], s);
+        rn[j] = s;
+    }
+    // block max -> one atomic (non-negative floats order like their bit patterns)
+    for (int o = 16; o > 0; o >>= 1) s = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, o));
+    if ((threadIdx.x & 31) == 0 && s > 0.f) atomicMax(rmax_bits, __float_as_uint(s));
+}
+
+// pad rows of width d to width dp (zero fill) so E1 only sees d in {16, 32}
+__global__ void knn_pad_kernel(const float* __restrict__ in, int n, int d, int dp, float* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)n * dp) return;
+    int row = (int)(i / dp), c = (int)(i % dp);
+    out[i] = c < d ? in[(size_t)row * d + c] : 0.f;
+}
+
+// ------------------------------------------------------------- SIMT candidate kernel
+// grid (ceil(nq/128), S); block 128: one query per thread, reference chunk tiled through smem.
+template <int D, int KC>
+__global__ void __launch_bounds__(128)
+knn_cand_simt_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r,
+                     const float* __restrict__ rn, int nr, int chunk, int maxdot,
+                     int32_t* __restrict__ cand_idx, float* __restrict__ cand_s, int S) {
+    constexpr int TR = 64;
+    __shared__ __align__(16) float sr[TR * D];
+    __shared__ float sn[TR];
+    const int qi = blockIdx.x * 128 + threadIdx.x;
+    const int c = blockIdx.y;
+    const int r0 = c * chunk;
+    const int r1 = min(nr, r0 + chunk);
+
+    float qv[D];
+    if (qi < nq) {
+        const float4* qp = reinterpret_cast<const float4*>(q + (size_t)qi * D);
+#pragma unroll
+        for (int t = 0; t < D / 4; ++t) {
+            float4 v = qp[t];
+            qv[4 * t] = v.x; qv[4 * t + 1] = v.y; qv[4 * t + 2] = v.z; qv[4 * t + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int t = 0; t < D; ++t) qv[t] = 0.f;
+    }
+    float bs[KC];
+    int bi[KC];
+#pragma unroll
+    for (int t = 0; t < KC; ++t) { bs[t] = INFINITY; bi[t] = -1; }
+
+    for (int base = r0; base < r1; base += TR) {
+        const int nt = min(TR, r1 - base);
+        __syncthreads();
+        const float4* src = reinterpret_cast<const float4*>(r + (size_t)base * D);
+        for (int t = threadIdx.x; t < nt * (D / 4); t += 128) reinterpret_cast<float4*>(sr)[t] = src[t];
+        if (threadIdx.x < nt) sn[threadIdx.x] = maxdot ? 0.f : rn[base + threadIdx.x];
+        __syncthreads();
+        for (int j = 0; j < nt; ++j) {
+            const float4* rp = reinterpret_cast<const float4*>(sr + j * D);
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int t = 0; t < D / 4; ++t) {
+                float4 v = rp[t];
+                a0 = fmaf(qv[4 * t], v.x, a0);
+                a1 = fmaf(qv[4 * t + 1], v.y, a1);
+                a0 = fmaf(qv[4 * t + 2], v.z, a0);
+                a1 = fmaf(qv[4 * t + 3], v.w, a1);
+            }
+            float dot = a0 + a1;
+            float s = maxdot ? -dot : fmaf(-2.f, dot, sn[j]);
+            if (s < bs[KC - 1]) {
+                bs[KC - 1] = s;
+                bi[KC - 1] = base + j;
+#pragma unroll
+                for (int t = KC - 1; t > 0; --t) {
+                    if (bs[t] < bs[t - 1]) {
+                        float fs = bs[t]; bs[t] = bs[t - 1]; bs[t - 1] = fs;
+                        int fi = bi[t]; bi[t] = bi[t - 1]; bi[t - 1] = fi;
+                    }
+                }
+            }
+        }
+    }
+    if (qi < nq) {
+        size_t o = ((size_t)qi * S + c) * KC;
+#pragma unroll
+        for (int t = 0; t < KC; ++t) { cand_idx[o + t] = bi[t]; cand_s[o + t] = bs[t]; }
+    }
+}
+
+// --------------------------------------------------------------------- exact re-rank
+__device__ __forceinline__ double knn_exact_key(const float* __restrict__ qp, const float* __restrict__ rp,
+                                                int d, int maxdot) {
+    // unfused, sequential over the feature axis: the same float64 operations as the oracle
+    double acc = 0.0;
+    if (maxdot) {
+        for (int c = 0; c < d; ++c) acc = __dadd_rn(acc, __dmul_rn((double)qp[c], (double)rp[c]));
+        return -acc;
+    }
+    for (int c = 0; c < d; ++c) {
+        double df = __dsub_rn((double)qp[c], (double)rp[c]);
+        acc = __dadd_rn(acc, __dmul_rn(df, df));
+    }
+    return acc;
+}
+
+__device__ __forceinline__ bool knn_less(double a, int ia, double b, int ib) {
+    return a < b || (a == b && ia < ib);
+}
+
+__device__ __forceinline__ float knn_out_dist(double key, int metric) {
+    if (metric == CB_KNN_L2) return sqrtf((float)key + 1e-7f);
+    if (metric == CB_KNN_MAXDOT) return (float)(-key);
+    return (float)key;
+}
+
+// one warp per query; ncand = S*KC <= 128 candidates (<= 4 per lane)
+__global__ void __launch_bounds__(256)
+knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int d, int dq_stride,
+                  int k, int metric, const int32_t* __restrict__ cand_idx, const float* __restrict__ cand_s,
+                  int S, int KC, const unsigned int* __restrict__ rmax_bits, double gamma,
+                  int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist,
+                  int32_t* __restrict__ fb_list, int* __restrict__ fb_count) {
+    const int lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (qi >= nq) return;
+    const int maxdot = metric == CB_KNN_MAXDOT;
+    const int ncand = S * KC;
+    const float* qp = q + (size_t)qi * dq_stride;
+    double key[4];
+    int id[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        int ci = lane + 32 * t;
+        id[t] = -1;
+        key[t] = INFINITY;
+        if (ci < ncand) {
+            int j = cand_idx[(size_t)qi * ncand + ci];
+            if (j >= 0) {
+                id[t] = j;
+                key[t] = knn_exact_key(qp, r + (size_t)j * dq_stride, d, maxdot);
+            }
+        }
+    }
+    double kth = 0.0;
+    int found = 0;
+    for (int round = 0; round < k; ++round) {
+        double bk = INFINITY;
+        int bj = 0x7fffffff, bt = -1;
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (id[t] >= 0 && knn_less(key[t], id[t], bk, bj)) { bk = key[t]; bj = id[t]; bt = t; }
+        double wk = bk;
+        int wj = bj;
+        for (int o = 16; o > 0; o >>= 1) {
+            double ok = __shfl_xor_sync(0xffffffffu, wk, o);
+            int oj = __shfl_xor_sync(0xffffffffu, wj, o);
+            if (knn_less(ok, oj, wk, wj)) { wk = ok; wj = oj; }
+        }
+        if (wj == 0x7fffffff) break;  // fewer than k candidates (cannot happen when k <= nr)
+        if (bt >= 0 && bj == wj) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (t == bt) id[t] = -1;
+        }
+        if (lane == 0) {
+            size_t o = (size_t)qi * k + round;
+            if (idx64) idx64[o] = wj;
+            if (idx32) idx32[o] = wj;
+            if (dist) dist[o] = knn_out_dist(wk, metric);
+        }
+        kth = wk;
+        ++found;
+    }
+    // proof obligation: nothing dropped by a chunk can beat the k-th exact key
+    double qn = 0.0;
+    for (int c = lane; c < d; c += 32) qn += (double)qp[c] * (double)qp[c];
+    for (int o = 16; o > 0; o >>= 1) qn += __shfl_xor_sync(0xffffffffu, qn, o);
+    const double rmax = (double)__uint_as_float(*rmax_bits);
+    double e, shift;
+    if (maxdot) {
+        e = gamma * sqrt(qn * rmax) + 1e-300;
+        shift = 0.0;
+    } else {
+        e = gamma * (rmax + 2.0 * sqrt(qn * rmax)) + 1e-300;
+        shift = qn * (1.0 - 1e-12);
+    }
+    bool bad = found < k;
+    for (int c = lane; c < S; c += 32) {
+        float w = cand_s[((size_t)qi * S + c) * KC + KC - 1];
+        if (!(w == INFINITY) && !((double)w - e + shift > kth)) bad = true;
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (bad && lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+}
+
+// exact float64 brute force for the queued rows: one block per row, k rounds of
+// "smallest (key,index) above the previous one"
+__global__ void __launch_bounds__(256)
+knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, int nr, int d, int stride,
+                    int k, int metric, const int32_t* __restrict__ fb_list, const int* __restrict__ fb_count,
+                    int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist) {
+    __shared__ double wk[8];
+    __shared__ int wj[8];
+    __shared__ double prev_k;
+    __shared__ int prev_j;
+    const int maxdot = metric == CB_KNN_MAXDOT;
+    const int n = *fb_count;
+    for (int e = blockIdx.x; e < n; e += gridDim.x) {
+        const int qi = fb_list[e];
+        const float* qp = q + (size_t)qi * stride;
+        if (threadIdx.x == 0) { prev_k = -INFINITY; prev_j = -1; }
+        __syncthreads();
+        for (int round = 0; round < k; ++round) {
+            const double pk = prev_k;
+            const int pj = prev_j;
+            double bk = INFINITY;
+            int bj = 0x7fffffff;
+            for (int j = threadIdx.x; j < nr; j += blockDim.x) {
+                double key = knn_exact_key(qp, r + (size_t)j * stride, d, maxdot);
+                if (knn_less(pk, pj, key, j) && knn_less(key, j, bk, bj)) { bk = key; bj = j; }
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                double ok = __shfl_xor_sync(0xffffffffu, bk, o);
+                int oj = __shfl_xor_sync(0xffffffffu, bj, o);
+                if (knn_less(ok, oj, bk, bj)) { bk = ok; bj = oj; }
+            }
+            if ((threadIdx.x & 31) == 0) { wk[threadIdx.x >> 5] = bk; wj[threadIdx.x >> 5] = bj; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+                    if (knn_less(wk[w], wj[w], bk, bj)) { bk = wk[w]; bj = wj[w]; }
+                size_t o = (size_t)qi * k + round;
+                if (bj != 0x7fffffff) {
+                    if (idx64) idx64[o] = bj;
+                    if (idx32) idx32[o] = bj;
+                    if (dist) dist[o] = knn_out_dist(bk, metric);
+                }
+                prev_k = bk;
+                prev_j = bj;
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------ host driver
+template <int D, int KC>
+static void launch_simt(const float* q, int nq, const float* r, const float* rn, int nr, int chunk, int S,
+                        int maxdot, int32_t* ci, float* cs, cudaStream_t st) {
+    dim3 grid(cb_div_up(nq, 128), S);
+    knn_cand_simt_kernel<D, KC><<<grid, 128, 0, st>>>(q, nq, r, rn, nr, chunk, maxdot, ci, cs, S);
+}
+
+const char* cb_knn_variant_name(const cb_ctx* ctx);
+
+int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k, int metric,
+                int64_t* idx, float* dist, int32_t* idx32, cudaStream_t st) {
+    if (nq == 0) return CB_OK;
+    if (!q || !r || nq < 0 || nr <= 0 || d <= 0 || d > 256 || k <= 0 || k > 64 || k > nr || metric < 0 ||
+        metric > 2)
+        CB_FAIL(ctx, CB_EINVAL, "cb_knn: bad arguments (nq=%d nr=%d d=%d k=%d metric=%d)", nq, nr, d, k,
+                metric);
+    if (d > 32 || k > 12) {
+        // Engine E2: exact rows + radix select
+        int m2 = metric == CB_KNN_MAXDOT ? 2 : 0;
+        int mode = metric == CB_KNN_L2 ? 1 : (metric == CB_KNN_MAXDOT ? 2 : 0);
+        return cb_rows_topk(ctx, q, nq, r, nr, d, k, m2, 0, 0, 0, idx, idx32, nullptr, dist, mode, nullptr,
+                            st);
+    }
+    const int dp = d <= 16 ? 16 : 32;
+    const int KC = k <= 5 ? 8 : 16;
+    // reference chunks: enough blocks for >= 2 waves, chunks of >= 256 refs, S*KC <= 128
+    int qblocks = cb_div_up(nq, 128);
+    int S = cb_div_up(2 * ctx->sm_count, qblocks);
+    S = max(1, min(S, 128 / KC));
+    S = min(S, max(1, nr / 256));
+    int chunk = cb_div_up(nr, S);
+    chunk = (chunk + 127) & ~127;  // whole tensor-core column tiles per chunk
+    S = cb_div_up(nr, chunk);
+
+    const float* qd = q;
+    const float* rd = r;
+    if (dp != d) {
+        float* qpad = cb_alloc_t<float>(ctx, (size_t)nq * dp);
+        float* rpad = cb_alloc_t<float>(ctx, (size_t)nr * dp);
+        if (!qpad || !rpad) return CB_ENOMEM;
+        knn_pad_kernel<<<cb_div_up((int)((size_t)nq * dp), 256), 256, 0, st>>>(q, nq, d, dp, qpad);
+        CB_LAUNCH_CHECK(ctx);
+        knn_pad_kernel<<<cb_div_up((int)((size_t)nr * dp), 256), 256, 0, st>>>(r, nr, d, dp, rpad);
+        CB_LAUNCH_CHECK(ctx);
+        qd = qpad;
+        rd = rpad;
+    }
+    float* rn = cb_alloc_t<float>(ctx, nr);
+    unsigned int* scal = cb_alloc_t<unsigned int>(ctx, 2);  // [0] rmax bits, [1] fallback count
+    int32_t* ci = cb_alloc_t<int32_t>(ctx, (size_t)nq * S * KC);
+    float* cs = cb_alloc_t<float>(ctx, (size_t)nq * S * KC);
+    int32_t* fb = cb_alloc_t<int32_t>(ctx, nq);
+    if (!rn || !scal || !ci || !cs || !fb) return CB_ENOMEM;
+    CB_CUDA(ctx, cudaMemsetAsync(scal, 0, 2 * sizeof(unsigned int), st));
+    knn_norms_kernel<<<cb_div_up(nr, 256), 256, 0, st>>>(rd, nr, dp, rn, scal);
+    CB_LAUNCH_CHECK(ctx);
+
+    const int maxdot = metric == CB_KNN_MAXDOT;
+    double gamma = (dp + 4) * 6.0e-8;
+    bool done = false;
+    if (ctx->knn_variant != 1) {
+        int rc = knn_cand_tc_launch(ctx, qd, nq, rd, rn, nr, dp, KC, chunk, S, maxdot, ci, cs, st);
+        if (rc == CB_OK) {
+            done = true;
+            gamma = knn_cand_tc_gamma(dp);
+        } else if (rc != CB_EUNSUPPORTED || ctx->knn_variant == 2) {
+            return rc;
+        }
+    }
+    if (!done) {
+        if (dp == 16 && KC == 8) launch_simt<16, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
+        else if (dp == 16) launch_simt<16, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
+        else if (KC == 8) launch_simt<32, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
+        else launch_simt<32, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
+        CB_LAUNCH_CHECK(ctx);
+    }
+    knn_rerank_kernel<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, dp, k, metric, ci, cs, S, KC, scal, gamma,
+                                                       idx, idx32, dist, fb, (int*)(scal + 1));
+    CB_LAUNCH_CHECK(ctx);
+    knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, dp, k, metric, fb,
+                                                                     (int*)(scal + 1), idx, idx32, dist);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
+    if (d > 32 || k > 12) return cb_rows_topk_workspace(nq, nr, k);
+    size_t b = 0;
+    b += cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nr * 32 * 4);  // pads
+    b += cb_align((size_t)nr * 4) + 256;
+    b += 2 * cb_align((size_t)nq * 128 * 4) + cb_align((size_t)nq * 4);
+    b += cb_align((size_t)(nq + nr) * 32 * 2 * 2) + (1 << 16);  // bf16 hi/lo operands of the tc variant
+    return b;
+}
+
+__global__ void knn_mutual_kernel(const int64_t* __restrict__ idx, int k, const int32_t* __restrict__ rev,
+                                  int nq, uint8_t* __restrict__ mutual) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nq) mutual[i] = rev[idx[(size_t)i * k]] == i;
+}
+
+extern "C" int cb_knn(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k, int metric,
+                      int64_t* idx, float* dist, uint8_t* mutual, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nq == 0) return CB_OK;
+    if (!idx) CB_FAIL(ctx, CB_EINVAL, "cb_knn: idx is null");
+    if (nq < 0 || nr <= 0 || d <= 0 || d > 256 || k <= 0 || k > nr)
+        CB_FAIL(ctx, CB_EINVAL, "cb_knn: bad shape (nq=%d nr=%d d=%d k=%d)", nq, nr, d, k);
+    size_t need = knn_workspace(ctx, nq, nr, d, k);
+    if (mutual) need += knn_workspace(ctx, nr, nq, d, 1) + cb_align((size_t)nr * 4);
+    if ((rc = cb_reserve(ctx, need))) return rc;
+    if ((rc = cb_knn_impl(ctx, q, nq, r, nr, d, k, metric, idx, dist, nullptr, st))) return rc;
+    if (mutual) {
+        int32_t* rev = cb_alloc_t<int32_t>(ctx, nr);
+        if (!rev) return CB_ENOMEM;
+        if ((rc = cb_knn_impl(ctx, r, nr, q, nq, d, 1, metric, nullptr, nullptr, rev, st))) return rc;
+        knn_mutual_kernel<<<cb_div_up(nq, 256), 256, 0, st>>>(idx, k, rev, nq, mutual);
+        CB_LAUNCH_CHECK(ctx);
+    }
+    return CB_OK;
+}
+
+extern "C" int cb_knn_ragged(cb_ctx* ctx, const float* q, const float* r, int d, int k, int metric,
+                             const int32_t* h_q_off, const int32_t* h_r_off, int n_problems, int64_t* idx,
+                             float* dist, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_problems < 0 || !h_q_off || !h_r_off) CB_FAIL(ctx, CB_EINVAL, "cb_knn_ragged: bad offsets");
+    size_t need = 0;
+    for (int p = 0; p < n_problems; ++p) {
+        int nq = h_q_off[p + 1] - h_q_off[p], nr = h_r_off[p + 1] - h_r_off[p];
+        if (nq < 0 || nr < 0 || (nq > 0 && k > nr))
+            CB_FAIL(ctx, CB_EINVAL, "cb_knn_ragged: problem %d has nq=%d nr=%d k=%d", p, nq, nr, k);
+        if (nq > 0) need += knn_workspace(ctx, nq, nr, d, k);
+    }
+    if ((rc = cb_reserve(ctx, need))) return rc;
+    for (int p = 0; p < n_problems; ++p) {
+        int nq = h_q_off[p + 1] - h_q_off[p], nr = h_r_off[p + 1] - h_r_off[p];
+        if (nq == 0) continue;
+        rc = cb_knn_impl(ctx, q + (size_t)h_q_off[p] * d, nq, r + (size_t)h_r_off[p] * d, nr, d, k, metric,
+                         idx + (size_t)h_q_off[p] * k, dist ? dist + (size_t)h_q_off[p] * k : nullptr,
+                         nullptr, st);
+        if (rc) return rc;
+    }
+    return CB_OK;
+}

@@ -1,0 +1,26 @@
+// Internal interfaces between knn.cu, knn_tc.cu and select.cu.
+#pragma once
+#include "common.cuh"
+
+// Candidate layout shared by both candidate variants: for query qi and reference chunk c
+// (references [c*chunk, min(nr,(c+1)*chunk))) the KC best approximate scores, ascending, at
+// cand_s[(qi*S + c)*KC + t] with their GLOBAL reference index in cand_idx (unused: -1 / +inf).
+
+// tcgen05 candidate pass (knn_tc.cu).  d in {16,32}.  Returns CB_EUNSUPPORTED when the shape is
+// outside what the tensor-core kernel covers (caller falls back to the SIMT kernel).
+int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr,
+                       int d, int KC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s,
+                       cudaStream_t st);
+// relative error bound of the tcgen05 split-bf16 inner product: |err| <= gamma * |q| |r|
+double knn_cand_tc_gamma(int d);
+
+// Engine E2 (select.cu): exact float64 rows + per-row radix select.
+//   metric: 0 squared L2 (unfused, sequential: bit-identical with the oracle), 1 Euclidean
+//   (sqrt of 0), 2 negative inner product, 3 cosine distance.
+//   Output rows sorted ascending by (value, index).  idx64/idx32/dist64/dist32 may each be NULL.
+//   sort_by_index != 0 returns the k selected indices in ascending INDEX order instead.
+int cb_rows_topk(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k, int metric,
+                 int exclude_self, int self_offset, int sort_by_index, int64_t* idx64, int32_t* idx32,
+                 double* dist64, float* dist32, int dist32_mode /*0 raw,1 sqrt(v+1e-7),2 -v*/,
+                 const int32_t* q_gather /*optional [nq] row ids into q*/, cudaStream_t st);
+size_t cb_rows_topk_workspace(int nq, int nr, int k);
