@@ -1,0 +1,156 @@
+// K4: Chamfer / nearest-neighbour distances in 3-D.
+// Replaces chamfer_kdtree_1direction(apply_transform(..)) (utils/preprocess.py:39-48,67-70),
+// chamfer_gpu / chamfer_gpu_1direction (:51-64) and pc_dist.chamfer / compute_dist
+// (utils/pc_dist.py:45-99) of the reference.
+//
+// The search runs in fp32 difference form (brute force, references tiled through shared
+// memory, packed (distance bits, index) atomicMin across reference chunks); the distance that
+// enters the mean is then recomputed in float64 for the chosen neighbour, so the result is
+// within ~1e-7 relative of the float64 KD-tree answer (contract: 1e-5).
+#include "common.cuh"
+
+#include <math.h>
+
+// brute-force NN: one x point per thread, y chunk tiled through shared memory; poses stay on the device
+__global__ void nn3_kernel(const float4* __restrict__ x, int nx, const float4* __restrict__ y, int ny,
+                           int chunk, unsigned long long* __restrict__ best) {
+    constexpr int TY = 256;
+    __shared__ float4 sy[TY];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y0 = blockIdx.y * chunk, y1 = min(ny, y0 + chunk);
+    float4 p = i < nx ? x[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    float bd = INFINITY;
+    int bj = 0;
+    for (int base = y0; base < y1; base += TY) {
+        const int nt = min(TY, y1 - base);
+        __syncthreads();
+        if (threadIdx.x < nt) sy[threadIdx.x] = y[base + threadIdx.x];
+        __syncthreads();
+#pragma unroll 8
+        for (int j = 0; j < nt; ++j) {
+            float4 v = sy[j];
+            float dx = p.x - v.x, dy = p.y - v.y, dz = p.z - v.z;
+            float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            if (d < bd) { bd = d; bj = base + j; }
+        }
+    }
+    if (i < nx && y1 > y0) {
+        unsigned long long key = ((unsigned long long)__float_as_uint(bd) << 32) | (unsigned int)bj;
+        atomicMin(&best[i], key);
+    }
+}
+
+__device__ __forceinline__ void apply_pose(const double* T, double& x, double& y, double& z) {
+    double tx = T[0] * x + T[1] * y + T[2] * z + T[3];
+    double ty = T[4] * x + T[5] * y + T[6] * z + T[7];
+    double tz = T[8] * x + T[9] * y + T[10] * z + T[11];
+    x = tx; y = ty; z = tz;
+}
+
+// exact float64 distance of every p to its chosen neighbour; per-block partial sum / max
+__global__ void __launch_bounds__(256)
+nn3_finalize_kernel(const float* __restrict__ p, int np, const double* __restrict__ Tp,
+                    const float* __restrict__ q, const double* __restrict__ Tq,
+                    const unsigned long long* __restrict__ best, double* __restrict__ partial_sum,
+                    double* __restrict__ partial_max, int32_t* __restrict__ nn_idx) {
+    __shared__ double ws[8], wm[8];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    double d = 0.0;
+    if (i < np) {
+        int j = (int)(best[i] & 0xffffffffull);
+        double x = p[3 * (size_t)i], y = p[3 * (size_t)i + 1], z = p[3 * (size_t)i + 2];
+        double u = q[3 * (size_t)j], v = q[3 * (size_t)j + 1], w = q[3 * (size_t)j + 2];
+        if (Tp) apply_pose(Tp, x, y, z);
+        if (Tq) apply_pose(Tq, u, v, w);
+        double dx = x - u, dy = y - v, dz = z - w;
+        d = sqrt(dx * dx + dy * dy + dz * dz);
+        if (nn_idx) nn_idx[i] = j;
+    }
+    double s = d, m = d;
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    }
+    if ((threadIdx.x & 31) == 0) { ws[threadIdx.x >> 5] = s; wm[threadIdx.x >> 5] = m; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { s += ws[w]; m = fmax(m, wm[w]); }
+        partial_sum[blockIdx.x] = s;
+        partial_max[blockIdx.x] = m;
+    }
+}
+
+// out[0] (+)= sum(partials)/n   or   max(partials)
+__global__ void nn3_reduce_kernel(const double* __restrict__ partial_sum, const double* __restrict__ partial_max,
+                                  int nblocks, int n, int mode /*0 mean set,1 mean add,2 max*/,
+                                  double* __restrict__ out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double s = 0.0, m = 0.0;
+    for (int b = 0; b < nblocks; ++b) { s += partial_sum[b]; m = fmax(m, partial_max[b]); }
+    if (mode == 0) out[0] = s / (double)n;
+    else if (mode == 1) out[0] += s / (double)n;
+    else out[0] = m;
+}
+
+__global__ void pack_points_dev_pose_kernel(const float* __restrict__ xyz, int n, const double* __restrict__ T,
+                                            float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double x = xyz[3 * (size_t)i], y = xyz[3 * (size_t)i + 1], z = xyz[3 * (size_t)i + 2];
+    if (T) apply_pose(T, x, y, z);
+    out[i] = make_float4((float)x, (float)y, (float)z, 0.f);
+}
+
+static int nn3_direction(cb_ctx* ctx, const float* p, int np, const double* Tp, const float4* p4,
+                         const float* q, int nq, const double* Tq, const float4* q4, int mode, double* out,
+                         int32_t* nn_idx, cudaStream_t st) {
+    unsigned long long* best = cb_alloc_t<unsigned long long>(ctx, np);
+    int nblk = cb_div_up(np, 256);
+    double* ps = cb_alloc_t<double>(ctx, nblk);
+    double* pm = cb_alloc_t<double>(ctx, nblk);
+    if (!best || !ps || !pm) return CB_ENOMEM;
+    CB_CUDA(ctx, cudaMemsetAsync(best, 0xff, (size_t)np * 8, st));
+    int S = cb_div_up(2 * ctx->sm_count, nblk);
+    S = max(1, min(S, cb_div_up(nq, 256)));
+    int chunk = cb_div_up(cb_div_up(nq, S), 256) * 256;
+    S = cb_div_up(nq, chunk);
+    nn3_kernel<<<dim3(nblk, S), 256, 0, st>>>(p4, np, q4, nq, chunk, best);
+    CB_LAUNCH_CHECK(ctx);
+    nn3_finalize_kernel<<<nblk, 256, 0, st>>>(p, np, Tp, q, Tq, best, ps, pm, nn_idx);
+    CB_LAUNCH_CHECK(ctx);
+    nn3_reduce_kernel<<<1, 32, 0, st>>>(ps, pm, nblk, np, mode, out);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+static int chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
+                        int two_dir, int use_max, double* out, int32_t* nn_idx, cudaStream_t st) {
+    if (!a || !b || !out || na <= 0 || nb <= 0) CB_FAIL(ctx, CB_EINVAL, "chamfer: empty cloud or null pointer");
+    int rc = cb_reserve(ctx, (size_t)(na + nb) * 40 + (1 << 16));
+    if (rc) return rc;
+    float4* a4 = cb_alloc_t<float4>(ctx, na);
+    float4* b4 = cb_alloc_t<float4>(ctx, nb);
+    if (!a4 || !b4) return CB_ENOMEM;
+    pack_points_dev_pose_kernel<<<cb_div_up(na, 256), 256, 0, st>>>(a, na, T, a4);
+    CB_LAUNCH_CHECK(ctx);
+    pack_points_dev_pose_kernel<<<cb_div_up(nb, 256), 256, 0, st>>>(b, nb, nullptr, b4);
+    CB_LAUNCH_CHECK(ctx);
+    rc = nn3_direction(ctx, a, na, T, a4, b, nb, nullptr, b4, use_max ? 2 : 0, out, nn_idx, st);
+    if (rc) return rc;
+    if (two_dir) rc = nn3_direction(ctx, b, nb, nullptr, b4, a, na, T, a4, 1, out, nullptr, st);
+    return rc;
+}
+
+extern "C" int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
+                          int two_dir, double* out, int32_t* nn_idx, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    return chamfer_impl(ctx, a, na, b, nb, T, two_dir, 0, out, nn_idx, (cudaStream_t)stream);
+}
+
+extern "C" int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
+                         double* out, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    return chamfer_impl(ctx, a, na, b, nb, T, 0, 1, out, nullptr, (cudaStream_t)stream);
+}
