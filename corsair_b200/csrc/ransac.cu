@@ -1,0 +1,474 @@
+// K3: correspondence RANSAC.
+// Replaces registration_based_on_corr (utils/eval_pose.py:82-100 of the reference), i.e.
+// Open3D's registration_ransac_based_on_correspondence(ransac_n=10, point-to-point without
+// scaling, RANSACConvergenceCriteria(100000, 0.999)) on an identity correspondence set
+// (SURVEY.md section 8a rows a8-a12).
+//
+// Stages per wave of hypotheses (all enqueued up front; a wave whose first hypothesis is at or
+// beyond the device-side budget exits immediately):
+//   fit    one thread per hypothesis: gather the minimal set (explicit, or the counter-based
+//          seeded draw), Umeyama without scale in float64 with a one-sided Jacobi 3x3 SVD
+//   score  block = 128 hypotheses (one per thread, pose in registers) x a slice of the
+//          correspondences streamed through shared memory as float4 pairs; fp32 evaluation,
+//          float64 unfused re-evaluation inside the rounding band around max_dist^2 so the
+//          inlier COUNT is exactly the float64 one
+//   fold   one warp folds the wave in hypothesis order with Open3D's "better" rule
+//          (count desc, rmse asc, first wins ties) and its adaptive budget update.
+#include "common.cuh"
+
+#include <math.h>
+
+struct RansacState {
+    int budget;       // hypotheses to evaluate in total (shrinks when adaptive)
+    int best_h;
+    int best_count;
+    int n_eval;
+    double best_sum;
+    double best_rmse;
+    double T[16];
+    unsigned int smax_bits;  // max |src| (fp32 bits), max |tgt|
+    unsigned int tmax_bits;
+};
+
+// -------------------------------------------------------------------------- pack
+__global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const float* __restrict__ tgt_xyz,
+                                   const int64_t* __restrict__ src_idx, const int64_t* __restrict__ tgt_idx,
+                                   int m, float4* __restrict__ src4, float4* __restrict__ tgt4,
+                                   RansacState* __restrict__ state) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float ns = 0.f, nt = 0.f;
+    if (i < m) {
+        size_t a = src_idx ? (size_t)src_idx[i] : (size_t)i;
+        size_t b = tgt_idx ? (size_t)tgt_idx[i] : (size_t)i;
+        float4 s = make_float4(src_xyz[3 * a], src_xyz[3 * a + 1], src_xyz[3 * a + 2], 0.f);
+        float4 t = make_float4(tgt_xyz[3 * b], tgt_xyz[3 * b + 1], tgt_xyz[3 * b + 2], 0.f);
+        src4[i] = s;
+        tgt4[i] = t;
+        ns = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z);
+        nt = sqrtf(t.x * t.x + t.y * t.y + t.z * t.z);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ns = fmaxf(ns, __shfl_xor_sync(0xffffffffu, ns, o));
+        nt = fmaxf(nt, __shfl_xor_sync(0xffffffffu, nt, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (ns > 0.f) atomicMax(&state->smax_bits, __float_as_uint(ns));
+        if (nt > 0.f) atomicMax(&state->tmax_bits, __float_as_uint(nt));
+    }
+}
+
+__global__ void ransac_init_kernel(RansacState* state, int h_total) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        state->budget = h_total;
+        state->best_h = -1;
+        state->best_count = 0;
+        state->n_eval = 0;
+        state->best_sum = 0.0;
+        state->best_rmse = 0.0;
+        for (int i = 0; i < 16; ++i) state->T[i] = (i % 5 == 0) ? 1.0 : 0.0;
+        state->smax_bits = 0;
+        state->tmax_bits = 0;
+    }
+}
+
+// --------------------------------------------------------------------------- fit
+// One-sided (Hestenes) Jacobi SVD of a 3x3 held column-wise in a[col][row]; on exit
+// a[:,j] = sigma_j u_j, v[:,j] = v_j.  Same algorithm as the oracle's C restatement.
+__device__ void jacobi3(double a[3][3], double v[3][3]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) v[i][j] = (i == j) ? 1.0 : 0.0;
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        int rotated = 0;
+#pragma unroll
+        for (int p = 0; p < 2; ++p)
+#pragma unroll
+            for (int q = p + 1; q < 3; ++q) {
+                double al = 0, be = 0, ga = 0;
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    al += a[p][r] * a[p][r];
+                    be += a[q][r] * a[q][r];
+                    ga += a[p][r] * a[q][r];
+                }
+                if (ga == 0.0 || fabs(ga) <= 1e-300 + 2.3e-16 * sqrt(al * be)) continue;
+                rotated = 1;
+                double zeta = (be - al) / (2.0 * ga);
+                double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    double x = a[p][r], y = a[q][r];
+                    a[p][r] = c * x - s * y;
+                    a[q][r] = s * x + c * y;
+                    x = v[p][r]; y = v[q][r];
+                    v[p][r] = c * x - s * y;
+                    v[q][r] = s * x + c * y;
+                }
+            }
+        if (!rotated) break;
+    }
+}
+
+__device__ __forceinline__ void cross3(const double* x, const double* y, double* o) {
+    o[0] = x[1] * y[2] - x[2] * y[1];
+    o[1] = x[2] * y[0] - x[0] * y[2];
+    o[2] = x[0] * y[1] - x[1] * y[0];
+}
+
+// Umeyama without scale (Eigen::umeyama as Open3D's TransformationEstimationPointToPoint uses
+// it): R = U diag(1,1,det(U)det(V)) V^T of Sigma = 1/n sum (t-mt)(s-ms)^T, t = mt - R ms.
+// T12 = [R | t] row-major 3x4.
+__device__ void umeyama_fit(const float4* __restrict__ src4, const float4* __restrict__ tgt4, const int* idx,
+                            int n, double* T12) {
+    double ms[3] = {0, 0, 0}, mt[3] = {0, 0, 0};
+    for (int i = 0; i < n; ++i) {
+        float4 s = src4[idx[i]], t = tgt4[idx[i]];
+        ms[0] += (double)s.x; ms[1] += (double)s.y; ms[2] += (double)s.z;
+        mt[0] += (double)t.x; mt[1] += (double)t.y; mt[2] += (double)t.z;
+    }
+    for (int r = 0; r < 3; ++r) { ms[r] /= n; mt[r] /= n; }
+    double a[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+    for (int i = 0; i < n; ++i) {
+        float4 s = src4[idx[i]], t = tgt4[idx[i]];
+        double ds[3] = {(double)s.x - ms[0], (double)s.y - ms[1], (double)s.z - ms[2]};
+        double dt[3] = {(double)t.x - mt[0], (double)t.y - mt[1], (double)t.z - mt[2]};
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int r = 0; r < 3; ++r) a[c][r] += dt[r] * ds[c];
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int r = 0; r < 3; ++r) a[c][r] /= n;
+    double v[3][3];
+    jacobi3(a, v);
+    double nr[3];
+    int o[3] = {0, 1, 2};
+    for (int c = 0; c < 3; ++c) nr[c] = sqrt(a[c][0] * a[c][0] + a[c][1] * a[c][1] + a[c][2] * a[c][2]);
+    for (int i = 0; i < 2; ++i)
+        for (int j = i + 1; j < 3; ++j)
+            if (nr[o[j]] > nr[o[i]]) { int tmp = o[i]; o[i] = o[j]; o[j] = tmp; }
+    double u1[3], u2[3], u3[3], v1[3], v2[3], v3[3], vx[3];
+    for (int r = 0; r < 3; ++r) { v1[r] = v[o[0]][r]; v2[r] = v[o[1]][r]; v3[r] = v[o[2]][r]; }
+    const double n1 = nr[o[0]], n2 = nr[o[1]];
+    if (n1 > 0) { for (int r = 0; r < 3; ++r) u1[r] = a[o[0]][r] / n1; }
+    else { u1[0] = 1; u1[1] = 0; u1[2] = 0; }
+    if (n2 > 1e-300 && n2 > 1e-14 * n1) {
+        for (int r = 0; r < 3; ++r) u2[r] = a[o[1]][r] / n2;
+        double d = u1[0] * u2[0] + u1[1] * u2[1] + u1[2] * u2[2];
+        for (int r = 0; r < 3; ++r) u2[r] -= d * u1[r];
+    } else {
+        int k = fabs(u1[0]) < fabs(u1[1]) ? (fabs(u1[0]) < fabs(u1[2]) ? 0 : 2)
+                                          : (fabs(u1[1]) < fabs(u1[2]) ? 1 : 2);
+        double e[3] = {0, 0, 0};
+        e[k] = 1;
+        cross3(u1, e, u2);
+    }
+    const double l2 = sqrt(u2[0] * u2[0] + u2[1] * u2[1] + u2[2] * u2[2]);
+    for (int r = 0; r < 3; ++r) u2[r] /= l2;
+    cross3(u1, u2, u3);
+    cross3(v1, v2, vx);
+    const double detv = vx[0] * v3[0] + vx[1] * v3[1] + vx[2] * v3[2];
+    const double sg = detv < 0 ? -1.0 : 1.0;
+    for (int r = 0; r < 3; ++r) {
+        double R0 = u1[r] * v1[0] + u2[r] * v2[0] + sg * u3[r] * v3[0];
+        double R1 = u1[r] * v1[1] + u2[r] * v2[1] + sg * u3[r] * v3[1];
+        double R2 = u1[r] * v1[2] + u2[r] * v2[2] + sg * u3[r] * v3[2];
+        T12[4 * r] = R0; T12[4 * r + 1] = R1; T12[4 * r + 2] = R2;
+        T12[4 * r + 3] = mt[r] - (R0 * ms[0] + R1 * ms[1] + R2 * ms[2]);
+    }
+}
+
+constexpr int kMaxRansacN = 16;
+
+__global__ void __launch_bounds__(128)
+ransac_fit_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m,
+                  const int32_t* __restrict__ minimal, uint64_t seed, int h0, int w, int ransac_n,
+                  const RansacState* __restrict__ state, double* __restrict__ Tw) {
+    if (state && h0 >= state->budget) return;
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= w) return;
+    const int h = h0 + j;
+    int idx[kMaxRansacN];
+    for (int t = 0; t < ransac_n; ++t)
+        idx[t] = minimal ? minimal[(size_t)h * ransac_n + t]
+                         : cb_draw_index(seed, (uint64_t)h * (uint64_t)ransac_n + (uint64_t)t, m);
+    double T12[12];
+    umeyama_fit(src4, tgt4, idx, ransac_n, T12);
+    for (int t = 0; t < 12; ++t) Tw[(size_t)j * 12 + t] = T12[t];
+}
+
+__global__ void ransac_draw_kernel(uint64_t seed, int m, size_t total, int32_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < total) out[i] = cb_draw_index(seed, (uint64_t)i, m);
+}
+
+// ------------------------------------------------------------------------- score
+// grid (ceil(w/128), P); block 128.  Thread = hypothesis, points streamed through smem.
+constexpr int kScoreTile = 256;
+
+__global__ void __launch_bounds__(128)
+ransac_score_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int split,
+                    const double* __restrict__ Tw, int h0, int w, double thr2d,
+                    const RansacState* __restrict__ state, int32_t* __restrict__ pc, double* __restrict__ ps) {
+    if (h0 >= state->budget) return;
+    __shared__ float4 ss[kScoreTile];
+    __shared__ float4 st[kScoreTile];
+    const int j = blockIdx.x * 128 + threadIdx.x;
+    const int jj = min(j, w - 1);
+    const double* Td = Tw + (size_t)jj * 12;
+    const float r00 = (float)Td[0], r01 = (float)Td[1], r02 = (float)Td[2], t0 = (float)Td[3];
+    const float r10 = (float)Td[4], r11 = (float)Td[5], r12 = (float)Td[6], t1 = (float)Td[7];
+    const float r20 = (float)Td[8], r21 = (float)Td[9], r22 = (float)Td[10], t2 = (float)Td[11];
+    // rounding band of the fp32 evaluation around thr^2 ("RANSAC exactness")
+    const float smax = __uint_as_float(state->smax_bits), tmax = __uint_as_float(state->tmax_bits);
+    const float tn = sqrtf(t0 * t0 + t1 * t1 + t2 * t2);
+    const float errv = 16.f * 5.9604645e-8f * (smax + tmax + tn);
+    const float thr2 = (float)thr2d;
+    const float band = 2.f * sqrtf(thr2) * errv + errv * errv + 8.f * 5.9604645e-8f * thr2;
+    const float lo = thr2 - band, hi = thr2 + band;
+
+    const int p0 = blockIdx.y * split, p1 = min(m, p0 + split);
+    int count = 0;
+    double sum = 0.0;
+    for (int base = p0; base < p1; base += kScoreTile) {
+        const int nt = min(kScoreTile, p1 - base);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nt; t += 128) {
+            ss[t] = src4[base + t];
+            st[t] = tgt4[base + t];
+        }
+        __syncthreads();
+        float fsum = 0.f;
+#pragma unroll 4
+        for (int t = 0; t < nt; ++t) {
+            const float4 s = ss[t];
+            const float4 q = st[t];
+            float e0 = fmaf(r00, s.x, fmaf(r01, s.y, fmaf(r02, s.z, t0 - q.x)));
+            float e1 = fmaf(r10, s.x, fmaf(r11, s.y, fmaf(r12, s.z, t1 - q.y)));
+            float e2 = fmaf(r20, s.x, fmaf(r21, s.y, fmaf(r22, s.z, t2 - q.z)));
+            float d2 = fmaf(e2, e2, fmaf(e1, e1, e0 * e0));
+            if (d2 < hi) {
+                if (d2 >= lo) {
+                    // inside the band: the oracle's float64 expression, unfused, same order
+                    double x = s.x, y = s.y, z = s.z;
+                    double f0 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[0], x), __dmul_rn(Td[1], y)), __dmul_rn(Td[2], z)), Td[3]), (double)q.x);
+                    double f1 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[4], x), __dmul_rn(Td[5], y)), __dmul_rn(Td[6], z)), Td[7]), (double)q.y);
+                    double f2 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[8], x), __dmul_rn(Td[9], y)), __dmul_rn(Td[10], z)), Td[11]), (double)q.z);
+                    double dd = __dadd_rn(__dadd_rn(__dmul_rn(f0, f0), __dmul_rn(f1, f1)), __dmul_rn(f2, f2));
+                    if (dd < thr2d) { ++count; fsum += (float)dd; }
+                } else {
+                    ++count;
+                    fsum += d2;
+                }
+            }
+        }
+        sum += (double)fsum;
+    }
+    if (j < w) {
+        pc[(size_t)blockIdx.y * w + j] = count;
+        ps[(size_t)blockIdx.y * w + j] = sum;
+    }
+}
+
+// -------------------------------------------------------------------------- fold
+__device__ int ransac_budget_from_count(int good, int m, int n, double conf, int cap) {
+    if (conf >= 1.0 || good <= 0) return cap;
+    double wr = (double)good / (double)m;
+    double denom = log(1.0 - pow(wr, (double)n));
+    if (denom == 0.0) return cap;
+    double k = log(1.0 - conf) / denom;
+    return k < (double)cap ? (int)ceil(k) : cap;
+}
+
+// one warp; folds hypotheses h0..h0+w-1 in order.
+__global__ void __launch_bounds__(32)
+ransac_fold_kernel(const int32_t* __restrict__ pc, const double* __restrict__ ps, int P, const double* __restrict__ Tw,
+                   int h0, int w, int m, int ransac_n, int adaptive, double conf, RansacState* __restrict__ state,
+                   int32_t* __restrict__ counts, double* __restrict__ sums) {
+    if (h0 >= state->budget) return;
+    const int lane = threadIdx.x;
+    int budget = state->budget;
+    int best_count = state->best_count, best_h = state->best_h;
+    double best_rmse = state->best_rmse, best_sum = state->best_sum;
+    int stop = 0, n_eval = state->n_eval;
+    for (int c0 = 0; c0 < w && !stop; c0 += 32) {
+        const int j = c0 + lane;
+        int cnt = 0;
+        double sm = 0.0;
+        if (j < w) {
+            for (int p = 0; p < P; ++p) {
+                cnt += pc[(size_t)p * w + j];
+                sm += ps[(size_t)p * w + j];
+            }
+        }
+        const double rm = cnt > 0 ? sqrt(sm / (double)cnt) : 0.0;
+        // candidates that could improve on the best known at chunk entry
+        bool cand = j < w && (cnt > best_count || (cnt == best_count && rm < best_rmse));
+        unsigned mask = __ballot_sync(0xffffffffu, cand);
+        const int valid = min(32, w - c0);
+        int processed = valid;
+        while (mask) {
+            int l = __ffs(mask) - 1;
+            mask &= mask - 1;
+            int h = h0 + c0 + l;
+            if (h >= budget) break;
+            int c = __shfl_sync(0xffffffffu, cnt, l);
+            double r = __shfl_sync(0xffffffffu, rm, l);
+            double s = __shfl_sync(0xffffffffu, sm, l);
+            if (c > best_count || (c == best_count && r < best_rmse)) {
+                best_count = c; best_rmse = r; best_sum = s; best_h = h;
+                if (lane < 12) state->T[(lane / 4) * 4 + (lane % 4)] = Tw[(size_t)(c0 + l) * 12 + lane];
+                if (adaptive) {
+                    int b = ransac_budget_from_count(c, m, ransac_n, conf, budget);
+                    if (b < budget) budget = b;
+                }
+            }
+        }
+        if (h0 + c0 + valid > budget) {
+            processed = max(0, budget - (h0 + c0));
+            stop = 1;
+        }
+        if (j < w && lane < processed) {
+            if (counts) counts[h0 + j] = cnt;
+            if (sums) sums[h0 + j] = sm;
+        }
+        n_eval = h0 + c0 + processed;
+    }
+    if (lane == 0) {
+        state->budget = budget;
+        state->best_count = best_count;
+        state->best_h = best_h;
+        state->best_rmse = best_rmse;
+        state->best_sum = best_sum;
+        state->n_eval = n_eval;
+    }
+}
+
+__global__ void ransac_finish_kernel(const RansacState* __restrict__ state, double* __restrict__ T,
+                                     double* __restrict__ stats) {
+    int i = threadIdx.x;
+    if (i < 16) T[i] = (i >= 12) ? (i == 15 ? 1.0 : 0.0) : state->T[i];
+    if (i == 0) {
+        stats[0] = state->best_h;
+        stats[1] = state->best_count;
+        stats[2] = state->best_sum;
+        stats[3] = state->n_eval;
+    }
+}
+
+// -------------------------------------------------------------------------- host
+__global__ void ransac_expand_T_kernel(const double* __restrict__ Tw, int h, double* __restrict__ T_all) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= h * 16) return;
+    int hh = i / 16, e = i % 16;
+    T_all[i] = e < 12 ? Tw[(size_t)hh * 12 + e] : (e == 15 ? 1.0 : 0.0);
+}
+
+static int ransac_wave_size(int wave_index) {
+    int w = 4096;
+    for (int i = 1; i < wave_index && w < 32768; ++i) w <<= 1;  // 4096, 4096, 8192, 16384, 32768, ...
+    return w;
+}
+
+extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const float* tgt_xyz, int n_tgt,
+                         const int64_t* src_idx, const int64_t* tgt_idx, int m, const int32_t* minimal,
+                         uint64_t seed, int h_total, int ransac_n, double max_dist, int adaptive,
+                         double confidence, double* T, double* stats, int32_t* counts, double* sums,
+                         void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!T || !stats || m < 0 || h_total < 0 || ransac_n > kMaxRansacN)
+        CB_FAIL(ctx, CB_EINVAL, "cb_ransac: bad arguments (m=%d h=%d n=%d)", m, h_total, ransac_n);
+    (void)n_src;
+    (void)n_tgt;
+    const int wmax = 32768;
+    const int P_max = 64;
+    size_t need = cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) +
+                  cb_align((size_t)wmax * 12 * 8) + cb_align((size_t)P_max * wmax * 4) +
+                  cb_align((size_t)P_max * wmax * 8);
+    if ((rc = cb_reserve(ctx, need))) return rc;
+    RansacState* state = cb_alloc_t<RansacState>(ctx, 1);
+    if (!state) return CB_ENOMEM;
+    ransac_init_kernel<<<1, 32, 0, st>>>(state, h_total);
+    CB_LAUNCH_CHECK(ctx);
+    // Open3D returns the default (identity, fitness 0) result for degenerate requests
+    const bool degenerate = ransac_n < 3 || m < ransac_n || max_dist <= 0.0 || h_total == 0;
+    if (!degenerate) {
+        if (!src_xyz || !tgt_xyz) CB_FAIL(ctx, CB_EINVAL, "cb_ransac: null point arrays");
+        float4* src4 = cb_alloc_t<float4>(ctx, m);
+        float4* tgt4 = cb_alloc_t<float4>(ctx, m);
+        double* Tw = cb_alloc_t<double>(ctx, (size_t)wmax * 12);
+        int32_t* pc = cb_alloc_t<int32_t>(ctx, (size_t)P_max * wmax);
+        double* ps = cb_alloc_t<double>(ctx, (size_t)P_max * wmax);
+        if (!src4 || !tgt4 || !Tw || !pc || !ps) return CB_ENOMEM;
+        ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, src_idx, tgt_idx, m, src4, tgt4,
+                                                              state);
+        CB_LAUNCH_CHECK(ctx);
+        const double thr2 = max_dist * max_dist;
+        int h0 = 0;
+        for (int wave = 0; h0 < h_total; ++wave) {
+            const int w = min(ransac_wave_size(wave), h_total - h0);
+            const int groups = cb_div_up(w, 128);
+            int P = cb_div_up(3 * ctx->sm_count, groups);
+            P = max(1, min(min(P, P_max), cb_div_up(m, kScoreTile)));
+            int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
+            P = cb_div_up(m, split);
+            ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
+                                                                 state, Tw);
+            CB_LAUNCH_CHECK(ctx);
+            ransac_score_kernel<<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state, pc,
+                                                                 ps);
+            CB_LAUNCH_CHECK(ctx);
+            ransac_fold_kernel<<<1, 32, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
+                                                 counts, sums);
+            CB_LAUNCH_CHECK(ctx);
+            h0 += w;
+        }
+    }
+    ransac_finish_kernel<<<1, 32, 0, st>>>(state, T, stats);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+extern "C" int cb_draw_minimal_sets(cb_ctx* ctx, uint64_t seed, int m, int h_total, int ransac_n, int32_t* out,
+                                    void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    if (!out || m <= 0 || h_total < 0 || ransac_n <= 0) CB_FAIL(ctx, CB_EINVAL, "cb_draw_minimal_sets: bad arguments");
+    size_t total = (size_t)h_total * ransac_n;
+    if (total == 0) return CB_OK;
+    ransac_draw_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, m, total, out);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+extern "C" int cb_fit_minimal(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, int m,
+                              const int32_t* minimal, int h_total, int ransac_n, double* T_all, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!src_xyz || !tgt_xyz || !minimal || !T_all || m <= 0 || h_total < 0 || ransac_n < 1 || ransac_n > kMaxRansacN)
+        CB_FAIL(ctx, CB_EINVAL, "cb_fit_minimal: bad arguments");
+    if (h_total == 0) return CB_OK;
+    if ((rc = cb_reserve(ctx, 2 * cb_align((size_t)m * 16) + cb_align((size_t)h_total * 96) + 4096))) return rc;
+    RansacState* state = cb_alloc_t<RansacState>(ctx, 1);
+    float4* src4 = cb_alloc_t<float4>(ctx, m);
+    float4* tgt4 = cb_alloc_t<float4>(ctx, m);
+    double* Tw = cb_alloc_t<double>(ctx, (size_t)h_total * 12);
+    if (!state || !src4 || !tgt4 || !Tw) return CB_ENOMEM;
+    ransac_init_kernel<<<1, 32, 0, st>>>(state, h_total);
+    CB_LAUNCH_CHECK(ctx);
+    ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, nullptr, nullptr, m, src4, tgt4, state);
+    CB_LAUNCH_CHECK(ctx);
+    ransac_fit_kernel<<<cb_div_up(h_total, 128), 128, 0, st>>>(src4, tgt4, m, minimal, 0, 0, h_total, ransac_n,
+                                                               nullptr, Tw);
+    CB_LAUNCH_CHECK(ctx);
+    ransac_expand_T_kernel<<<cb_div_up(h_total * 16, 256), 256, 0, st>>>(Tw, h_total, T_all);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
