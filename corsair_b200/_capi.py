@@ -1,0 +1,163 @@
+"""ctypes binding of libcorsair_b200.so (the C ABI in include/corsair_b200.h).
+
+PyTorch is used only as the device allocator / stream provider: every kernel lives in the
+shared library.  There is no CPU fallback: if the library or a CUDA device is missing, calls
+raise ``RuntimeError``.
+"""
+import ctypes
+import os
+import threading
+
+import numpy as np
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libcorsair_b200.so")
+
+_lib = None
+_lib_lock = threading.Lock()
+
+c_void_p, c_int, c_double, c_u64, c_size_t = (ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
+                                              ctypes.c_uint64, ctypes.c_size_t)
+
+# name -> (restype, argtypes); mirrors include/corsair_b200.h
+SIGNATURES = {
+    "cb_version": (c_int, []),
+    "cb_create": (c_int, [ctypes.POINTER(c_void_p), c_int, c_size_t]),
+    "cb_destroy": (c_int, [c_void_p]),
+    "cb_last_error": (ctypes.c_char_p, [c_void_p]),
+    "cb_launch_count": (ctypes.c_int64, [c_void_p]),
+    "cb_knn_variant": (ctypes.c_char_p, [c_void_p]),
+    "cb_set_knn_variant": (c_int, [c_void_p, c_int]),
+    "cb_knn": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                       c_void_p, c_void_p, c_void_p]),
+    "cb_knn_ragged": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                              c_int, c_void_p, c_void_p, c_void_p]),
+    "cb_pdist": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "cb_dot_matrix": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "cb_retrieval_topk": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int,
+                                  c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "cb_ransac": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
+                          c_void_p, c_u64, c_int, c_int, c_double, c_int, c_double, c_void_p,
+                          c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cb_draw_minimal_sets": (c_int, [c_void_p, c_u64, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "cb_fit_minimal": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p,
+                               c_void_p]),
+    "cb_chamfer": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                           c_void_p, c_void_p]),
+    "cb_chamfer_matrix": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "cb_nn_max": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "cb_feature_rows_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+                                     c_void_p, c_void_p]),
+    "cb_kmeans_batch": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
+                                c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "cb_assign_labels": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                                 c_void_p]),
+    "cb_irls_pose": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+}
+
+
+def load_library():
+    """dlopen the extension (no GPU needed for this step) and declare every signature."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                    "g.build()'` (there is no CPU fallback)")
+            lib = ctypes.CDLL(LIB_PATH)
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(lib, name)
+                fn.restype = res
+                fn.argtypes = args
+            _lib = lib
+    return _lib
+
+
+class CorsairError(RuntimeError):
+    pass
+
+
+_STATUS_EXC = {-1: ValueError, -4: NotImplementedError}
+
+
+class Context:
+    """One cb_ctx (device workspace) bound to a device; use one per host thread."""
+
+    def __init__(self, device=0, workspace_bytes=256 << 20):
+        if not torch.cuda.is_available():
+            raise RuntimeError("corsair_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = load_library()
+        self.device = torch.device("cuda", device)
+        torch.cuda.init()
+        with torch.cuda.device(self.device):
+            torch.zeros(1, device=self.device)  # make sure the primary context exists
+            h = c_void_p()
+            rc = self.lib.cb_create(ctypes.byref(h), device, workspace_bytes)
+        if rc != 0 or not h:
+            raise RuntimeError(f"cb_create failed with status {rc}")
+        self.handle = h
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.cb_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def call(self, name, *args):
+        rc = getattr(self.lib, name)(self.handle, *args)
+        if rc != 0:
+            msg = self.lib.cb_last_error(self.handle).decode("utf-8", "replace")
+            raise _STATUS_EXC.get(rc, CorsairError)(f"{name}: {msg} (status {rc})")
+
+    def launches(self):
+        return int(self.lib.cb_launch_count(self.handle))
+
+    def knn_variant(self):
+        return self.lib.cb_knn_variant(self.handle).decode()
+
+    def set_knn_variant(self, v):
+        self.lib.cb_set_knn_variant(self.handle, int(v))
+
+    # -- marshalling helpers --------------------------------------------------------------
+    def dev(self, x, dtype):
+        """numpy / torch (any device) -> contiguous torch tensor of `dtype` on this device."""
+        if isinstance(x, torch.Tensor):
+            t = x.detach()
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(x))
+        return t.to(device=self.device, dtype=dtype, non_blocking=False).contiguous()
+
+    def empty(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+
+def ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+_tls = threading.local()
+
+
+def get_context(device=None):
+    """Thread-local context for `device` (default: the current CUDA device)."""
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    if isinstance(device, torch.device):
+        device = device.index or 0
+    cache = getattr(_tls, "ctx", None)
+    if cache is None:
+        cache = _tls.ctx = {}
+    if device not in cache:
+        cache[device] = Context(device)
+    return cache[device]
