@@ -108,6 +108,22 @@ def ransac(src, tgt, max_dist, minimal_sets, adaptive=False, confidence=0.999,
     return out
 
 
+def splitmix64(x):
+    """splitmix64 finaliser on a uint64 array (wrapping arithmetic)."""
+    x = (x + np.uint64(0x9E3779B97F4A7C15)).astype(np.uint64)
+    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return x ^ (x >> np.uint64(31))
+
+
 def draw_minimal_sets(M, H, ransac_n=10, seed=0):
-    """The shared convention for seeded minimal sets."""
-    return np.random.default_rng(seed).integers(0, M, (H, ransac_n), dtype=np.int32)
+    """The repo-wide convention for seeded minimal sets (include/corsair_b200.h,
+    cb_draw_minimal_sets): counter-based, uniform with replacement over [0, M):
+        set[h][j] = (hi32(splitmix64(seed*0x9E3779B97F4A7C15 + h*ransac_n + j)) * M) >> 32
+    It replaces Open3D's shared-RNG-inside-OpenMP stream, which is not reproducible."""
+    with np.errstate(over="ignore"):
+        c = np.arange(H * ransac_n, dtype=np.uint64)
+        base = np.array([seed & 0xFFFFFFFFFFFFFFFF], dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+        x = splitmix64(base + c)
+        idx = ((x >> np.uint64(32)) * np.uint64(M)) >> np.uint64(32)
+    return idx.astype(np.int32).reshape(H, ransac_n)
