@@ -160,11 +160,11 @@ int cb_feature_rows_topk(cb_ctx* ctx, const float* feat, int n, int d, const int
  * gathered xyz, :216) + the acceptance statistics of :218-236.  rng_first [n_init] int32 and
  * rng_unif [n_init,K-1,n_trials] float64 are the data-independent draws of sklearn's
  * k-means++ (generated by the host shim from numpy RandomState).  Outputs per sample:
- * centers [n_samples,K,3] float32, stats [n_samples,4] float32 = {min centre distance, max
+ * centers [n_samples,K,3] float32, stats [n_samples,4] float64 = {min centre distance, max
  * mean intra-cluster error, std of label ratios over all n points, inertia}. */
 int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx, int n_samples,
                     int n_nn, int K, const int32_t* rng_first, const double* rng_unif, int n_init,
-                    int n_trials, float* centers, float* stats, void* stream);
+                    int n_trials, float* centers, double* stats, void* stream);
 
 /* KMeans.predict over all n points (:224,:240): labels [n] int32 nearest of K centres
  * (centers [K,3] float32), counts [K] int32 histogram (may be NULL). */
