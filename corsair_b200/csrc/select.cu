@@ -65,7 +65,7 @@ rows_kernel(const float* __restrict__ q, const int32_t* __restrict__ q_gather, i
         if (metric == 1) v = sqrt(v);
         else if (metric == 2) v = -v;
         else if (metric == 3) v = 1.0 - v / (sqrt(nq2[i]) * sqrt(nr2));
-        if (exclude_self && j == q0 + ql + self_offset) v = INFINITY;
+        if (exclude_self && j == q0 + ql + self_offset) v = exclude_self == 2 ? 0.0 : INFINITY;
         out[(size_t)ql * nr + j] = v;
     }
 }
@@ -205,8 +205,8 @@ int cb_rows_topk(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, in
                  int exclude_self, int self_offset, int sort_by_index, int64_t* idx64, int32_t* idx32,
                  double* dist64, float* dist32, int dist32_mode, const int32_t* q_gather, cudaStream_t st) {
     if (nq == 0) return CB_OK;
-    if (k <= 0 || k > nr - (exclude_self ? 1 : 0))
-        CB_FAIL(ctx, CB_EINVAL, "top-k: k=%d outside [1,%d]", k, nr - (exclude_self ? 1 : 0));
+    if (k <= 0 || k > nr - (exclude_self == 1 ? 1 : 0))
+        CB_FAIL(ctx, CB_EINVAL, "top-k: k=%d outside [1,%d]", k, nr - (exclude_self == 1 ? 1 : 0));
     int kcap = 32;
     while (kcap < k) kcap <<= 1;
     if (kcap > 16384) CB_FAIL(ctx, CB_EUNSUPPORTED, "top-k: k=%d above the 16384 the sort network holds", k);
