@@ -1,0 +1,211 @@
+"""Drop-in for the hot functions of the reference's utils/symmetry.py: split_corr (:145-179),
+symmetric_cut4 (:182-259) and sym_pose (:262-358).  The four visualisation helpers of that file
+need a graphics stack and are out of scope.
+
+Everything numeric runs in the C-ABI library: feature kNN (cb_knn / cb_knn_ragged),
+correspondence RANSAC (cb_ransac), one-direction Chamfer (cb_chamfer) and the three device pieces
+of the symmetry segmentation (cb_feature_rows_topk, cb_kmeans_batch, cb_assign_labels).  Host code
+only draws the 100 seed points from the global NumPy RNG exactly like the reference, replays the
+(data-independent) RandomState(0) stream sklearn's k-means++ would consume, and applies the
+sequential acceptance rule to 100 rows of statistics.
+"""
+import functools
+
+import numpy as np
+import torch
+from tqdm import tqdm
+
+from . import _capi
+from ._capi import ptr
+from .eval_pose import *  # noqa: F401,F403  (the reference re-exports these: utils/symmetry.py:33)
+from .eval_pose import find_kcorr, ransac_device
+from .preprocess import *  # noqa: F401,F403
+
+N_NN = 50        # utils/symmetry.py:214
+N_INIT = 10      # KMeans(..., n_init=10), utils/symmetry.py:216
+MIN_CENTER = 0.15  # utils/symmetry.py:234
+
+
+@functools.lru_cache(maxsize=None)
+def _kmeanspp_draws(n_nn, K, n_init=N_INIT):
+    """The draws sklearn's KMeans(random_state=0, n_init) k-means++ takes from RandomState(0) for
+    n_nn equally weighted samples: per init one ``choice`` (first centre) and K-1 ``uniform``
+    vectors of 2+int(log(K)) local trials.  They do not depend on the data."""
+    rs = np.random.RandomState(0)
+    sw = np.ones(n_nn, dtype=np.float32)
+    p = sw / sw.sum()
+    n_trials = 2 + int(np.log(K))
+    first = np.zeros(n_init, np.int32)
+    unif = np.zeros((n_init, max(K - 1, 1), n_trials), np.float64)
+    for i in range(n_init):
+        first[i] = rs.choice(n_nn, p=p)
+        for c in range(1, K):
+            unif[i, c - 1] = rs.uniform(size=n_trials)
+    return first, unif, n_trials
+
+
+def split_corr(pcsA, pcsB, featsA, featsB, knn, subsample_size=1000):
+    """utils/symmetry.py:145-179."""
+    xyzA_corrs, xyzB_corrs = [], []
+    for pcA, pcB, featA, featB in zip(pcsA, pcsB, featsA, featsB):
+        idx_0, idx_1 = find_kcorr(featA, featB, k=knn, subsample_size=subsample_size)
+        xyzA_corrs.append(pcA[idx_0])
+        xyzB_corrs.append(pcB[idx_1])
+    return np.concatenate(xyzA_corrs, axis=0), np.concatenate(xyzB_corrs, axis=0)
+
+
+def cut_model_device(feat_d, xyz_d, K, random_points, ctx):
+    """Device part of symmetric_cut4 for the sampled seed rows.  Returns (centers [S,K,3] f32,
+    stats [S,4] f64, nn_idx [S,n_nn] i32) as CUDA tensors."""
+    n, d = feat_d.shape
+    S = len(random_points)
+    n_nn = min(N_NN, n)
+    first, unif, n_trials = _kmeanspp_draws(n_nn, K)
+    samp = ctx.dev(np.asarray(random_points, dtype=np.int32), torch.int32)
+    nn_idx = ctx.empty((S, n_nn), torch.int32)
+    ctx.call("cb_feature_rows_topk", ptr(feat_d), n, d, ptr(samp), S, n_nn, ptr(nn_idx), ctx.stream)
+    first_d = ctx.dev(first, torch.int32)
+    unif_d = ctx.dev(unif, torch.float64)
+    centers = ctx.empty((S, K, 3), torch.float32)
+    stats = ctx.empty((S, 4), torch.float64)
+    ctx.call("cb_kmeans_batch", ptr(xyz_d), n, ptr(nn_idx), S, n_nn, K, ptr(first_d), ptr(unif_d), N_INIT,
+             n_trials, ptr(centers), ptr(stats), ctx.stream)
+    return centers, stats, nn_idx
+
+
+def select_cut(stats):
+    """The sequential acceptance rule of utils/symmetry.py:234-236 over the per-sample statistics
+    (min centre distance, max intra-cluster error, std of label ratios).  -1: no model."""
+    curr_var, win = 100, -1
+    for i, (dmin, emax, sd, _) in enumerate(stats):
+        if dmin > MIN_CENTER > emax and curr_var > sd:
+            curr_var, win = sd, i
+    return win
+
+
+def _masks_device(feat_d, xyz_d, K, max_sample, ctx):
+    if K not in (2, 4):
+        raise ValueError("not defined")
+    n = xyz_d.shape[0]
+    random_points = np.random.choice(n, max_sample, replace=False)  # global RNG, utils/symmetry.py:193
+    centers, stats, _ = cut_model_device(feat_d, xyz_d, K, random_points, ctx)
+    win = select_cut(stats.cpu().numpy())
+    if win < 0:
+        # the reference dereferences curr_model = None here (utils/symmetry.py:238)
+        raise AttributeError("'NoneType' object has no attribute 'cluster_centers_'")
+    c = centers[win].contiguous()
+    labels = ctx.empty((n,), torch.int32)
+    ctx.call("cb_assign_labels", ptr(xyz_d), n, ptr(c), K, ptr(labels), None, ctx.stream)
+    if K == 2:
+        order = [0, 1]
+    else:
+        ch = c.cpu().numpy()
+        dist = np.linalg.norm(ch[None, :, :] - ch[:, None, :], 2, 2)
+        dist[np.arange(K), np.arange(K)] = 100
+        rank_centers = np.argsort(dist[0, 1:])
+        order = [0, rank_centers[0] + 1, rank_centers[2] + 1, rank_centers[1] + 1]
+    return [labels == int(o) for o in order]
+
+
+def symmetric_cut4(feat, raw_pc, K, max_sample=100):
+    """utils/symmetry.py:182-259 -> list of K boolean NumPy masks over the N points."""
+    ctx = _capi.get_context()
+    feat_d = ctx.dev(feat, torch.float32)
+    xyz_d = ctx.dev(raw_pc, torch.float32)
+    return [m.cpu().numpy() for m in _masks_device(feat_d, xyz_d, K, max_sample, ctx)]
+
+
+def _segment_perm(masks):
+    """Concatenated ascending point indices of each segment and the segment offsets."""
+    parts = [torch.nonzero(m, as_tuple=False).reshape(-1) for m in masks]
+    off = np.zeros(len(parts) + 1, np.int32)
+    off[1:] = np.cumsum([int(p.numel()) for p in parts])
+    return parts, off
+
+
+def _pairing_ransac(ctx, F0s, A_perm, q_off, posF_d, B_parts, xyz0_d, xyz1_d, k_nn, max_corr, seed, ransac_kw):
+    """One symmetry pairing: per-segment kNN (ragged), concatenated correspondences, RANSAC."""
+    B_perm = torch.cat(B_parts)
+    r_off = np.zeros(len(B_parts) + 1, np.int32)
+    r_off[1:] = np.cumsum([int(p.numel()) for p in B_parts])
+    F1s = posF_d[B_perm].contiguous()
+    nq = int(q_off[-1])
+    idx = ctx.empty((nq, k_nn), torch.int64)
+    ctx.call("cb_knn_ragged", ptr(F0s), ptr(F1s), F0s.shape[1], k_nn, 0,
+             q_off.ctypes.data_as(_capi.c_void_p), r_off.ctypes.data_as(_capi.c_void_p), len(B_parts),
+             ptr(idx), None, ctx.stream)
+    seg_of_q = torch.repeat_interleave(torch.arange(len(B_parts), device=ctx.device),
+                                       torch.as_tensor(np.diff(q_off), device=ctx.device))
+    base = torch.as_tensor(r_off[:-1].astype(np.int64), device=ctx.device)[seg_of_q]
+    tgt_idx = B_perm[(idx + base[:, None]).reshape(-1)]
+    src_idx = torch.repeat_interleave(A_perm, k_nn)
+    return ransac_device(xyz0_d, xyz1_d, max_corr, seed, src_idx=src_idx, tgt_idx=tgt_idx, ctx=ctx, **ransac_kw)
+
+
+def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *, n_hypotheses=100000,
+             adaptive=True):
+    """utils/symmetry.py:262-358: pose with and without the symmetry-aided pairing search.
+
+    Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success)."""
+    ctx = _capi.get_context()
+    dev = ctx.device
+    baseF_d = ctx.dev(baseF, torch.float32)
+    posF_d = ctx.dev(posF, torch.float32)
+    xyz0_d = ctx.dev(xyz0, torch.float32)
+    xyz1_d = ctx.dev(xyz1, torch.float32)
+    n0 = baseF_d.shape[0]
+    rkw = dict(n_hypotheses=n_hypotheses, adaptive=adaptive)
+
+    def chamfer_of(T64):
+        # the reference rounds the pose to float32 before the Chamfer evaluation (:274,:280)
+        T32 = T64.to(torch.float32)
+        out = ctx.empty((1,), torch.float64)
+        Td = T32.to(torch.float64).contiguous()
+        ctx.call("cb_chamfer", ptr(xyz0_d), n0, ptr(xyz1_d), xyz1_d.shape[0], ptr(Td), 0, ptr(out), None,
+                 ctx.stream)
+        return T32, out
+
+    # vanilla: full-cloud kNN -> RANSAC -> Chamfer (:267-283)
+    idx = ctx.empty((n0, k_nn), torch.int64)
+    if posF_d.shape[0] < k_nn:
+        raise ValueError(f"k_nn={k_nn} exceeds the {posF_d.shape[0]} target points")
+    ctx.call("cb_knn", ptr(baseF_d), n0, ptr(posF_d), posF_d.shape[0], baseF_d.shape[1], k_nn, 0, ptr(idx),
+             None, None, ctx.stream)
+    src_idx = torch.repeat_interleave(torch.arange(n0, device=dev), k_nn)
+    res = ransac_device(xyz0_d, xyz1_d, max_corr, seed, src_idx=src_idx, tgt_idx=idx.reshape(-1), ctx=ctx, **rkw)
+    cands = [chamfer_of(res["T"])]
+
+    try:
+        K = 4 if pos_sym >= 2 else 2
+        base_masks = _masks_device(baseF_d, xyz0_d, K, 100, ctx)
+        pos_masks = _masks_device(posF_d, xyz1_d, K, 100, ctx)
+    except Exception as e:  # same swallow-and-fallback as utils/symmetry.py:299-301
+        tqdm.write(f"symmetry failed use ransac: {e}")
+        T_r, ch_r = cands[0]
+        T_r, ch_r = T_r.cpu(), float(ch_r.item())
+        return T_r, ch_r, T_r, ch_r, False
+
+    A_parts, q_off = _segment_perm(base_masks)
+    A_perm = torch.cat(A_parts)
+    F0s = baseF_d[A_perm].contiguous()
+    B_parts = [torch.nonzero(m, as_tuple=False).reshape(-1) for m in pos_masks]
+
+    def sweep(parts):
+        for _ in range(len(parts)):
+            r = _pairing_ransac(ctx, F0s, A_perm, q_off, posF_d, parts, xyz0_d, xyz1_d, k_nn, max_corr, seed, rkw)
+            cands.append(chamfer_of(r["T"]))
+            parts.append(parts.pop(0))
+        return parts
+
+    B_parts = sweep(B_parts)
+    if pos_sym >= 2:
+        B_parts = sweep([B_parts[0], B_parts[3], B_parts[2], B_parts[1]])
+
+    chamf = torch.cat([c for _, c in cands]).cpu().numpy()  # the one synchronisation of the sweep
+    best = 0
+    for i in range(1, len(cands)):
+        if chamf[best] > chamf[i]:  # strictly lower Chamfer wins (:321,:353)
+            best = i
+    T_ransac = cands[0][0].cpu()
+    T_best = cands[best][0].cpu()
+    return T_best, float(chamf[best]), T_ransac, float(chamf[0]), True
