@@ -10,8 +10,10 @@ pytestmark = pytest.mark.gpu
 
 def cloud(rng, n):
     p = rng.standard_normal((n, 3)).astype(np.float32)
-    p -= p.mean(0)
-    return (p / np.linalg.norm(p, axis=1).max()).astype(np.float32)
+    if n > 1:
+        p -= p.mean(0)
+        p /= np.linalg.norm(p, axis=1).max()
+    return p.astype(np.float32)
 
 
 def rigid(rng):
