@@ -17,7 +17,7 @@ chamfer_matrix_kernel(const float* __restrict__ pts, int L, int P, int row0, dou
     const int i = row0 + blockIdx.y, j = blockIdx.x;
     double* o = out + (size_t)blockIdx.y * L + j;
     if (i == j) {
-        if (threadIdx.x == 0) *o = 100.0;  // table = eye * 100 (utils/pc_dist.py:66)
+        if (threadIdx.x == 0) *o = 200.0;  // eye * 100, then table += table.T (utils/pc_dist.py:66,98)
         return;
     }
     const float* pa = pts + (size_t)i * P * 3;

@@ -16,9 +16,9 @@ def chamfer(pc0, pc1):
 
 
 def compute_chamfer(base_idx, pc0, pcs, domain, table):
-    """utils/pc_dist.py:55-58: fill table[base_idx, j] for j in domain."""
-    for j in domain:
-        table[base_idx, j] = chamfer(pc0, pcs[j])
+    """utils/pc_dist.py:55-58: fill table[base_idx, i] for i in [domain[0], domain[1])."""
+    for i in range(domain[0], domain[1]):
+        table[base_idx, i] = chamfer(pc0, pcs[i])
 
 
 def chamfer_rows_device(pts, row0=0, row1=None, ctx=None):
@@ -33,7 +33,7 @@ def chamfer_rows_device(pts, row0=0, row1=None, ctx=None):
 
 
 def compute_dist(pcs):
-    """utils/pc_dist.py:61-99 -> [L,L] float64 NumPy, symmetric, diagonal 100.
+    """utils/pc_dist.py:61-99 -> [L,L] float64 NumPy, symmetric, diagonal 200 (eye*100 + its transpose).
 
     Clouds of equal size go through the all-pairs kernel; ragged lists fall back to one
     cb_chamfer call per pair (still on the device)."""
@@ -44,7 +44,7 @@ def compute_dist(pcs):
         return chamfer_rows_device(stack.float()).cpu().numpy()
     table = np.eye(L) * 100
     for i in range(L):
-        compute_chamfer(i, pcs[i], pcs, range(i + 1, L), table)
+        compute_chamfer(i, pcs[i], pcs, [i + 1, L], table)
     table += table.T
     return table
 

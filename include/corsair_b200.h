@@ -141,7 +141,7 @@ int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, cons
 
 /* All-pairs two-direction Chamfer rows of compute_dist (utils/pc_dist.py:61-99):
  * pts [L,P,3] float32; out [(row1-row0), L] float64 rows row0..row1-1 of the full symmetric
- * table with diagonal 100. */
+ * table; the diagonal is 200 (eye*100 doubled by `table += table.T`, :66,:98). */
 int cb_chamfer_matrix(cb_ctx* ctx, const float* pts, int L, int P, int row0, int row1, double* out,
                       void* stream);
 

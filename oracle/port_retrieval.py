@@ -78,7 +78,7 @@ def compute_mAP(descriptors, gt_labels):
 
 
 def compute_dist(pcs):
-    """utils/pc_dist.py:61-99 without the thread fan-out: upper triangle, += T, diag 100."""
+    """utils/pc_dist.py:61-99 without the thread fan-out: upper triangle, += T (diagonal 200)."""
     L = len(pcs)
     table = np.eye(L) * 100
     for i in range(L):

@@ -49,7 +49,7 @@ def test_chamfer_two_direction_and_matrix(ctx, rng):
     assert abs(pc_dist.chamfer(pcs[2], pcs[3]).item() - ref[2, 3]) <= 1e-5 * ref[2, 3]
     table = pc_dist.compute_dist(pcs)
     assert table.shape == (6, 6) and table.dtype == np.float64
-    assert np.array_equal(table, table.T) and np.all(np.diag(table) == 100)
+    assert np.array_equal(table, table.T) and np.all(np.diag(table) == 200)
     np.testing.assert_allclose(table, ref, rtol=1e-5)
 
 
