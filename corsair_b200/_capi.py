@@ -29,6 +29,10 @@ SIGNATURES = {
     "cb_launch_count": (ctypes.c_int64, [c_void_p]),
     "cb_knn_variant": (ctypes.c_char_p, [c_void_p]),
     "cb_set_knn_variant": (c_int, [c_void_p, c_int]),
+    "cb_timing_enable": (c_int, [c_void_p, c_int]),
+    "cb_timing_read": (c_int, [c_void_p, c_int, ctypes.POINTER(c_double), ctypes.POINTER(c_double),
+                               ctypes.POINTER(ctypes.c_int64)]),
+    "cb_timing_reset": (c_int, [c_void_p]),
     "cb_knn": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                        c_void_p, c_void_p, c_void_p]),
     "cb_knn_ragged": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
@@ -128,6 +132,24 @@ class Context:
 
     def set_knn_variant(self, v):
         self.lib.cb_set_knn_variant(self.handle, int(v))
+
+    TIMING_CLASSES = ("knn_candidates", "knn_rerank", "ransac_score", "ransac_fit", "chamfer_nn",
+                      "rows_select", "kmeans")
+
+    def timing(self, on):
+        self.lib.cb_timing_enable(self.handle, int(bool(on)))
+
+    def timing_reset(self):
+        self.call("cb_timing_reset")
+
+    def timing_read(self):
+        """{class: (device ms, algorithmic work, launches)} -- synchronises the device."""
+        out = {}
+        for i, name in enumerate(self.TIMING_CLASSES):
+            ms, work, n = c_double(), c_double(), ctypes.c_int64()
+            self.call("cb_timing_read", i, ctypes.byref(ms), ctypes.byref(work), ctypes.byref(n))
+            out[name] = (ms.value, work.value, n.value)
+        return out
 
     # -- marshalling helpers --------------------------------------------------------------
     def dev(self, x, dtype):

@@ -29,6 +29,13 @@ extern "C" int cb_create(cb_ctx** out, int device, size_t workspace_bytes) {
         return CB_ENOMEM;
     }
     ctx->arena_bytes = workspace_bytes;
+    if (cudaMalloc(&ctx->dev_work, CB_TIMING_CLASSES * sizeof(double)) != cudaSuccess ||
+        cudaMemset(ctx->dev_work, 0, CB_TIMING_CLASSES * sizeof(double)) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(ctx->arena);
+        delete ctx;
+        return CB_ENOMEM;
+    }
     *out = ctx;
     return CB_OK;
 }
@@ -37,6 +44,9 @@ extern "C" int cb_destroy(cb_ctx* ctx) {
     if (!ctx) return CB_EINVAL;
     cudaSetDevice(ctx->device);
     if (ctx->arena) cudaFree(ctx->arena);
+    if (ctx->dev_work) cudaFree(ctx->dev_work);
+    for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
+    for (auto e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;
     return CB_OK;
 }
@@ -87,4 +97,73 @@ void* cb_alloc(cb_ctx* ctx, size_t bytes) {
     void* p = ctx->arena + ctx->arena_off;
     ctx->arena_off += bytes;
     return p;
+}
+
+// ------------------------------------------------------------------ bench instrumentation
+static cudaEvent_t take_event(cb_ctx* ctx) {
+    if (!ctx->event_pool.empty()) {
+        cudaEvent_t e = ctx->event_pool.back();
+        ctx->event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+cb_timed_scope::cb_timed_scope(cb_ctx* c, int cls, double work, cudaStream_t s) : ctx(c), st(s), on(c->timing) {
+    if (!on) return;
+    t.cls = cls;
+    t.work = work;
+    t.e0 = take_event(ctx);
+    t.e1 = take_event(ctx);
+    cudaEventRecord(t.e0, st);
+}
+
+cb_timed_scope::~cb_timed_scope() {
+    if (!on) return;
+    cudaEventRecord(t.e1, st);
+    ctx->timed.push_back(t);
+}
+
+static int timing_drain(cb_ctx* ctx) {
+    CB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CB_CUDA(ctx, cudaDeviceSynchronize());
+    for (auto& t : ctx->timed) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t.e0, t.e1) == cudaSuccess) ctx->cls_ms[t.cls] += ms;
+        ctx->cls_work[t.cls] += t.work;
+        ctx->cls_launches[t.cls] += 1;
+        ctx->event_pool.push_back(t.e0);
+        ctx->event_pool.push_back(t.e1);
+    }
+    ctx->timed.clear();
+    return CB_OK;
+}
+
+extern "C" int cb_timing_enable(cb_ctx* ctx, int on) {
+    if (!ctx) return CB_EINVAL;
+    ctx->timing = on != 0;
+    return CB_OK;
+}
+
+extern "C" int cb_timing_read(cb_ctx* ctx, int cls, double* ms, double* work, int64_t* launches) {
+    if (!ctx || cls < 0 || cls >= CB_TIMING_CLASSES) return CB_EINVAL;
+    int rc = timing_drain(ctx);
+    if (rc) return rc;
+    double dev[CB_TIMING_CLASSES];
+    CB_CUDA(ctx, cudaMemcpy(dev, ctx->dev_work, sizeof(dev), cudaMemcpyDeviceToHost));
+    if (ms) *ms = ctx->cls_ms[cls];
+    if (work) *work = ctx->cls_work[cls] + dev[cls];
+    if (launches) *launches = ctx->cls_launches[cls];
+    return CB_OK;
+}
+
+extern "C" int cb_timing_reset(cb_ctx* ctx) {
+    if (!ctx) return CB_EINVAL;
+    int rc = timing_drain(ctx);
+    if (rc) return rc;
+    for (int i = 0; i < CB_TIMING_CLASSES; ++i) { ctx->cls_ms[i] = 0; ctx->cls_work[i] = 0; ctx->cls_launches[i] = 0; }
+    CB_CUDA(ctx, cudaMemset(ctx->dev_work, 0, CB_TIMING_CLASSES * sizeof(double)));
+    return CB_OK;
 }

@@ -114,8 +114,11 @@ static int nn3_direction(cb_ctx* ctx, const float* p, int np, const double* Tp, 
     S = max(1, min(S, cb_div_up(nq, 256)));
     int chunk = cb_div_up(cb_div_up(nq, S), 256) * 256;
     S = cb_div_up(nq, chunk);
-    nn3_kernel<<<dim3(nblk, S), 256, 0, st>>>(p4, np, q4, nq, chunk, best);
-    CB_LAUNCH_CHECK(ctx);
+    {
+        cb_timed_scope ts(ctx, CB_T_CHAMFER_NN, 8.0 * np * (double)nq, st);
+        nn3_kernel<<<dim3(nblk, S), 256, 0, st>>>(p4, np, q4, nq, chunk, best);
+        CB_LAUNCH_CHECK(ctx);
+    }
     nn3_finalize_kernel<<<nblk, 256, 0, st>>>(p, np, Tp, q, Tq, best, ps, pm, nn_idx);
     CB_LAUNCH_CHECK(ctx);
     nn3_reduce_kernel<<<1, 32, 0, st>>>(ps, pm, nblk, np, mode, out);

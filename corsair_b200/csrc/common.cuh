@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/corsair_b200.h"
 
 struct cb_ctx {
@@ -16,6 +18,25 @@ struct cb_ctx {
     int64_t launches = 0;
     int knn_variant = 0;        // 0 auto, 1 simt, 2 tcgen05
     char err[512] = {0};
+    // bench instrumentation (cb_timing_*): CUDA-event brackets around the tracked kernel classes
+    bool timing = false;
+    struct TimedLaunch { int cls; double work; cudaEvent_t e0, e1; };
+    std::vector<TimedLaunch> timed;
+    std::vector<cudaEvent_t> event_pool;
+    double cls_ms[CB_TIMING_CLASSES] = {0};
+    double cls_work[CB_TIMING_CLASSES] = {0};
+    int64_t cls_launches[CB_TIMING_CLASSES] = {0};
+    double* dev_work = nullptr;  // [CB_TIMING_CLASSES] device-side work counters (RANSAC waves that ran)
+};
+
+// Bracket one tracked launch with events when timing is on.
+struct cb_timed_scope {
+    cb_ctx* ctx;
+    cudaStream_t st;
+    cb_ctx::TimedLaunch t;
+    bool on;
+    cb_timed_scope(cb_ctx* c, int cls, double work, cudaStream_t s);
+    ~cb_timed_scope();
 };
 
 #define CB_FAIL(ctx, code, ...)                                  \

@@ -329,6 +329,8 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     const int maxdot = metric == CB_KNN_MAXDOT;
     double gamma = (dp + 4) * 6.0e-8;
     bool done = false;
+    {
+    cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
     if (ctx->knn_variant != 1) {
         int rc = knn_cand_tc_launch(ctx, qd, nq, rd, rn, nr, dp, KC, chunk, S, maxdot, ci, cs, st);
         if (rc == CB_OK) {
@@ -345,6 +347,8 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
         else launch_simt<32, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         CB_LAUNCH_CHECK(ctx);
     }
+    }
+    cb_timed_scope tscope2(ctx, CB_T_KNN_RERANK, 0.0, st);
     knn_rerank_kernel<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, dp, k, metric, ci, cs, S, KC, scal, gamma,
                                                        idx, idx32, dist, fb, (int*)(scal + 1));
     CB_LAUNCH_CHECK(ctx);

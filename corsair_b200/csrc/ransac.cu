@@ -288,9 +288,10 @@ __device__ int ransac_budget_from_count(int good, int m, int n, double conf, int
 __global__ void __launch_bounds__(32)
 ransac_fold_kernel(const int32_t* __restrict__ pc, const double* __restrict__ ps, int P, const double* __restrict__ Tw,
                    int h0, int w, int m, int ransac_n, int adaptive, double conf, RansacState* __restrict__ state,
-                   int32_t* __restrict__ counts, double* __restrict__ sums) {
+                   int32_t* __restrict__ counts, double* __restrict__ sums, double* __restrict__ dev_work) {
     if (h0 >= state->budget) return;
     const int lane = threadIdx.x;
+    if (lane == 0) dev_work[CB_T_RANSAC_SCORE] += (double)w * (double)m * 32.0;  // bytes this wave streamed
     int budget = state->budget;
     int best_count = state->best_count, best_h = state->best_h;
     double best_rmse = state->best_rmse, best_sum = state->best_sum;
@@ -418,14 +419,20 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
             P = max(1, min(min(P, P_max), cb_div_up(m, kScoreTile)));
             int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
             P = cb_div_up(m, split);
-            ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
-                                                                 state, Tw);
-            CB_LAUNCH_CHECK(ctx);
-            ransac_score_kernel<<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state, pc,
-                                                                 ps);
-            CB_LAUNCH_CHECK(ctx);
+            {
+                cb_timed_scope ts(ctx, CB_T_RANSAC_FIT, 0.0, st);
+                ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
+                                                                     state, Tw);
+                CB_LAUNCH_CHECK(ctx);
+            }
+            {
+                cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
+                ransac_score_kernel<<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state,
+                                                                     pc, ps);
+                CB_LAUNCH_CHECK(ctx);
+            }
             ransac_fold_kernel<<<1, 32, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
-                                                 counts, sums);
+                                                 counts, sums, ctx->dev_work);
             CB_LAUNCH_CHECK(ctx);
             h0 += w;
         }

@@ -298,6 +298,7 @@ extern "C" int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32
     size_t smem = sizeof(KmWarp) * n_init;
     cudaError_t e = cudaFuncSetAttribute(kmeans_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "smem opt-in failed: %s", cudaGetErrorString(e));
+    cb_timed_scope ts(ctx, CB_T_KMEANS, 0.0, (cudaStream_t)stream);
     kmeans_batch_kernel<<<n_samples, 32 * n_init, smem, (cudaStream_t)stream>>>(
         xyz, n, nn_idx, n_nn, K, rng_first, rng_unif, n_init, n_trials, centers, stats);
     CB_LAUNCH_CHECK(ctx);

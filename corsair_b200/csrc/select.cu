@@ -223,6 +223,7 @@ int cb_rows_topk(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, in
     if (!rows) return CB_ENOMEM;
     for (int q0 = 0; q0 < nq; q0 += rows_per) {
         int nqc = min(rows_per, nq - q0);
+        cb_timed_scope ts(ctx, CB_T_ROWS_SELECT, (double)nqc * nr * d * 4.0, st);
         dim3 grid(cb_div_up(nr, 32), cb_div_up(nqc, 32));
         rows_kernel<<<grid, dim3(32, 8), 0, st>>>(q, q_gather, q0, nqc, r, nr, d, metric, exclude_self,
                                                   self_offset, rows);

@@ -59,6 +59,25 @@ const char* cb_knn_variant(const cb_ctx* ctx);
 /* force a kNN candidate variant (0 = auto, 1 = simt fp32, 2 = tcgen05 bf16x3); for tests/bench */
 int cb_set_knn_variant(cb_ctx* ctx, int variant);
 
+/* ---- instrumentation for bench.py ---------------------------------------------------------
+ * With timing enabled every launch of a tracked kernel class is bracketed by CUDA events on the
+ * launching stream.  cb_timing_read synchronises the device and returns, per class, the summed
+ * device time (ms), the algorithmic work launched (flop for the kNN candidate kernel, bytes for
+ * RANSAC scoring: hypotheses actually scored x correspondences x 32 B) and the launch count. */
+enum cb_timing_class {
+    CB_T_KNN_CAND = 0,   /* kNN candidate pass (distance GEMM + running top-k) */
+    CB_T_KNN_RERANK = 1, /* exact float64 re-rank + fallback */
+    CB_T_RANSAC_SCORE = 2,
+    CB_T_RANSAC_FIT = 3,
+    CB_T_CHAMFER_NN = 4,
+    CB_T_ROWS_SELECT = 5, /* exact rows + radix select (retrieval, 50-NN rows) */
+    CB_T_KMEANS = 6,
+    CB_TIMING_CLASSES = 8
+};
+int cb_timing_enable(cb_ctx* ctx, int on);
+int cb_timing_read(cb_ctx* ctx, int cls, double* ms, double* work, int64_t* launches);
+int cb_timing_reset(cb_ctx* ctx);
+
 /* ---- K1: feature-space kNN -------------------------------------------------------------
  * Replaces find_nn_cpu / find_knn_cpu (utils/find_nn.py:34-49, scipy KDTree in float64, the
  * kNN the shipped pipeline runs at utils/eval_pose.py:68,71) and find_nn_gpu / find_knn_gpu
