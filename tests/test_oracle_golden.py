@@ -1,0 +1,134 @@
+"""CPU: the oracle (oracle/port*.py) against the golden vectors produced by the reference's own
+code (tests/golden/make_golden.py).  This is what pins the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import port, port_retrieval, port_symmetry, ransac_c, ransac_np
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return np.load(os.path.join(G, name + ".npz"), allow_pickle=False)
+
+
+@pytest.mark.parametrize("d", [16, 32])
+def test_find_nn(d):
+    g = load("find_nn")
+    F0, F1 = g[f"F0_{d}"], g[f"F1_{d}"]
+    idx, d2 = port.find_knn_exact(F0, F1, 5)
+    assert np.array_equal(idx, g[f"knn_cpu_idx_{d}"])          # scipy KD-tree == canonical exact kNN
+    np.testing.assert_allclose(np.sqrt(d2), g[f"knn_cpu_dist_{d}"], rtol=1e-12)
+    assert np.array_equal(port.find_knn_cpu(F0, F1, 5), g[f"knn_cpu_idx_{d}"])
+    assert np.array_equal(port.find_nn_cpu(F0, F1), g[f"nn_cpu_idx_{d}"])
+    t0, t1 = torch.from_numpy(F0), torch.from_numpy(F1)
+    gi, gd = port.find_knn_gpu(t0, t1, 5, nn_max_n=300, return_distance=True)
+    assert np.array_equal(gi.numpy(), g[f"knn_gpu_idx_{d}"]) and np.array_equal(gd.numpy(), g[f"knn_gpu_dist_{d}"])
+    ni, nd = port.find_nn_gpu(t0, t1, nn_max_n=300, return_distance=True, dist_type="L2")
+    assert np.array_equal(ni.numpy(), g[f"nn_gpu_idx_{d}"]) and np.array_equal(nd.numpy(), g[f"nn_gpu_dist_{d}"])
+    assert np.array_equal(port.pdist(t0[:50], t1[:60], "L2").numpy(), g[f"pdist_L2_{d}"])
+    # the fp32 broadcast top-k of find_knn_gpu and the float64 KD-tree agree on these inputs
+    assert np.array_equal(g[f"knn_gpu_idx_{d}"].reshape(-1, 5), g[f"knn_cpu_idx_{d}"])
+    with pytest.raises(NotImplementedError):
+        port.pdist(t0, t1, "cosine")
+
+
+def test_find_kcorr():
+    g = load("find_nn")
+    i0, i1 = port.find_kcorr(g["F0_16"], g["F1_16"], k=5)
+    assert np.array_equal(i0, g["kcorr_idx0"]) and np.array_equal(i1, g["kcorr_idx1"])
+
+
+def test_chamfer():
+    g = load("chamfer")
+    a, b, c, T = g["a"], g["b"], g["c"], torch.from_numpy(g["T"])
+    ta = port.apply_transform(a, T)
+    np.testing.assert_allclose(ta, g["apply_transform"], rtol=0, atol=1e-15)
+    assert port.chamfer_kdtree_1direction(ta, b) == pytest.approx(float(g["kdtree_1dir"]), rel=1e-14)
+    pa, pb = torch.from_numpy(a), torch.from_numpy(b)
+    assert port.chamfer_gpu_1direction(pa, pb) == pytest.approx(float(g["gpu_1dir"]), rel=1e-6)
+    assert port.chamfer_gpu(pa, pb).item() == pytest.approx(float(g["gpu_2dir"]), rel=1e-6)
+    table = port_retrieval.compute_dist([torch.from_numpy(x) for x in (a, b, c)])
+    np.testing.assert_allclose(table, g["table"], rtol=1e-6)
+    assert np.all(np.diag(g["table"]) == 200)  # eye*100 doubled by table += table.T
+
+
+def test_retrieval():
+    g = load("retrieval")
+    st = port_retrieval.scan2cad_retrieval_eval(g["q"], g["lib"], g["best_match"], g["table"], 30)
+    assert np.array_equal(np.array(st["top1_predict"]), g["top1_predict"]) and np.array_equal(np.array(st["gt"]), g["gt"])
+    assert st["precision"] == pytest.approx(float(g["precision"]), rel=1e-12)
+    assert st["top1_error"] == pytest.approx(float(g["top1_error"]), rel=1e-12)
+    assert np.array_equal(port_retrieval.get_rank(g["lib"], 10), g["get_rank"])
+    ev = port_retrieval.retrieval_eval(g["lib"], 0.1, g["table"])
+    assert ev["mAP"] == pytest.approx(float(g["eval_mAP"]), rel=1e-9)
+    assert ev["percision"] == pytest.approx(float(g["eval_percision"]), rel=1e-12)
+    assert ev["top1_error"] == pytest.approx(float(g["eval_top1"]), rel=1e-12)
+    m = port_retrieval.compute_mAP(g["lib"], g["labels"])
+    assert m[0] == pytest.approx(float(g["mAP_instance"]), rel=1e-9)
+    np.testing.assert_allclose(np.array(m[1]), g["mAP_class"], rtol=1e-9)
+
+
+def test_irls():
+    g = load("irls")
+    p0, p1, w = (torch.from_numpy(g[k]) for k in ("p0", "p1", "w"))
+    x = torch.tensor([[0.04], [-0.02], [0.06], [0.02], [-0.03], [0.01]])
+    assert np.allclose(port_retrieval.get_trans(x).numpy(), g["get_trans"], atol=1e-7)
+    assert np.allclose(port_retrieval.est_quad_linear_robust(p0, p1).numpy(), g["T_unweighted"], atol=1e-5)
+    assert np.allclose(port_retrieval.est_quad_linear_robust(p0, p1, w).numpy(), g["T_weighted"], atol=1e-5)
+
+
+@pytest.mark.parametrize("cat,K", [("chair", 2), ("table", 4)])
+def test_symmetric_cut4(cat, K):
+    g = load("symmetry")
+    np.random.seed(31)
+    masks = port_symmetry.symmetric_cut4(g[f"{cat}_F"], g[f"{cat}_xyz"], K)
+    assert np.array_equal(np.stack(masks), g[f"{cat}_masks"])
+
+
+def test_eval_pose_and_sym_pose():
+    g = load("symmetry")
+    Te = torch.from_numpy(g["T_est"])
+    np.testing.assert_allclose(np.array(port.eval_pose(Te, g["T0"], g["T1"], 1)), g["eval_pose_sym1"], rtol=1e-6)
+    np.testing.assert_allclose(np.array(port.eval_pose(Te, g["T0"], g["T1"], 4)), g["eval_pose_sym4"], rtol=1e-6)
+    assert port.eval_pose(Te, g["T0"], g["T1"], 0) == (np.inf, np.inf)
+
+    def reg(src, tgt, max_corr, seed):
+        ms = ransac_np.draw_minimal_sets(len(src), 100000, 10, seed)
+        return ransac_c.ransac(src, tgt, max_corr, ms, adaptive=True)["T"]
+
+    np.random.seed(31)
+    Tb, cb, Tr, cr, ok = port_symmetry.sym_pose(g["sp_baseF"], g["sp_xyz0"], g["sp_posF"], g["sp_xyz1"], 1, k_nn=5,
+                                                max_corr=0.2, seed=31, registration=reg)
+    assert ok == bool(g["sp_ok"])
+    assert np.allclose(Tr.numpy(), g["sp_T_ransac"], atol=1e-6) and cr == pytest.approx(float(g["sp_ch_ransac"]), rel=1e-9)
+    assert np.allclose(Tb.numpy(), g["sp_T_best"], atol=1e-6) and cb == pytest.approx(float(g["sp_ch_best"]), rel=1e-9)
+
+
+def test_ransac_restatements_agree():
+    g = load("ransac_restated")
+    src, tgt, ms = g["src"], g["tgt"], g["minimal_sets"]
+    assert np.array_equal(ransac_np.draw_minimal_sets(2000, 256, 10, seed=3), ms)
+    for impl in (ransac_np, ransac_c):
+        r = impl.ransac(src, tgt, 0.2, ms, adaptive=False, return_all=True)
+        assert np.array_equal(np.asarray(r["counts"]), g["counts"])
+        np.testing.assert_allclose(r["sums"], g["sums"], rtol=1e-12)
+        assert r["best_h"] == int(g["best_h"]) and r["inliers"] == int(g["inliers"])
+        np.testing.assert_allclose(r["T"], g["T"], atol=1e-12)
+    a = ransac_np.ransac(src, tgt, 0.2, ms, adaptive=True)
+    b = ransac_c.ransac(src, tgt, 0.2, ms, adaptive=True)
+    assert a["best_h"] == b["best_h"] and a["n_evaluated"] == b["n_evaluated"] and a["inliers"] == b["inliers"]
+    # known-answer property: a noiseless rigid motion is recovered exactly and every point is an inlier
+    T = np.eye(4)
+    T[:3, :3] = np.array([[0, -1, 0], [1, 0, 0], [0, 0, 1.0]])
+    T[:3, 3] = [0.3, -0.2, 0.5]
+    s = src.astype(np.float64)
+    t = s @ T[:3, :3].T + T[:3, 3]
+    r = ransac_np.ransac(s, t, 0.05, ms[:4], adaptive=False)
+    assert r["inliers"] == len(s) and np.allclose(r["T"], T, atol=1e-12)
+    # degenerate requests return Open3D's default result
+    r = ransac_c.ransac(s[:5], t[:5], 0.2, ms[:4] % 5, adaptive=False)
+    assert r["best_h"] == -1 and np.array_equal(r["T"], np.eye(4))
