@@ -1,0 +1,103 @@
+"""GPU parity against the golden vectors the REFERENCE's own code produced (tests/golden)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return np.load(os.path.join(G, name + ".npz"), allow_pickle=False)
+
+
+@pytest.mark.parametrize("d", [16, 32])
+def test_find_nn_golden(ctx, d):
+    from corsair_b200 import eval_pose, find_nn
+    g = load("find_nn")
+    F0, F1 = g[f"F0_{d}"], g[f"F1_{d}"]
+    idx, dist = find_nn.find_knn_cpu(F0, F1, 5, return_distance=True)
+    assert np.array_equal(idx, g[f"knn_cpu_idx_{d}"])
+    np.testing.assert_allclose(dist, g[f"knn_cpu_dist_{d}"], rtol=2e-6)
+    assert np.array_equal(find_nn.find_nn_cpu(F0, F1), g[f"nn_cpu_idx_{d}"])
+    t0, t1 = torch.from_numpy(F0), torch.from_numpy(F1)
+    gi, gd = find_nn.find_knn_gpu(t0, t1, 5, nn_max_n=300, return_distance=True)
+    assert np.array_equal(gi.numpy(), g[f"knn_gpu_idx_{d}"])
+    np.testing.assert_allclose(gd.numpy(), g[f"knn_gpu_dist_{d}"], rtol=1e-5, atol=1e-7)
+    ni, nd = find_nn.find_nn_gpu(t0, t1, nn_max_n=300, return_distance=True, dist_type="L2")
+    assert np.array_equal(ni.numpy(), g[f"nn_gpu_idx_{d}"])
+    np.testing.assert_allclose(nd.numpy(), g[f"nn_gpu_dist_{d}"], rtol=1e-5)
+    np.testing.assert_allclose(find_nn.pdist(t0[:50], t1[:60], "L2").numpy(), g[f"pdist_L2_{d}"], rtol=1e-5)
+    if d == 16:
+        i0, i1 = eval_pose.find_kcorr(F0, F1, k=5)
+        assert np.array_equal(i0, g["kcorr_idx0"]) and np.array_equal(i1, g["kcorr_idx1"])
+
+
+def test_chamfer_golden(ctx):
+    from corsair_b200 import pc_dist, preprocess
+    g = load("chamfer")
+    a, b, c, T = g["a"], g["b"], g["c"], torch.from_numpy(g["T"])
+    np.testing.assert_allclose(preprocess.apply_transform(a, T), g["apply_transform"], atol=1e-15)
+    ref = float(g["kdtree_1dir"])
+    assert abs(preprocess.chamfer_device(a, b, T).item() - ref) <= 1e-5 * ref
+    assert abs(preprocess.chamfer_kdtree_1direction(g["apply_transform"], b) - ref) <= 1e-5 * ref
+    pa, pb = torch.from_numpy(a), torch.from_numpy(b)
+    assert abs(preprocess.chamfer_gpu_1direction(pa, pb) - float(g["gpu_1dir"])) <= 1e-5 * float(g["gpu_1dir"])
+    assert abs(preprocess.chamfer_gpu(pa, pb).item() - float(g["gpu_2dir"])) <= 1e-5 * float(g["gpu_2dir"])
+    np.testing.assert_allclose(pc_dist.compute_dist([pa, pb, torch.from_numpy(c)]), g["table"], rtol=1e-5)
+
+
+def test_retrieval_golden(ctx):
+    from corsair_b200 import retrieval
+    g = load("retrieval")
+    st = retrieval.scan2cad_retrieval_eval(g["q"], g["lib"], g["best_match"], g["table"], 30)
+    assert np.array_equal(np.array(st["top1_predict"]), g["top1_predict"]) and np.array_equal(np.array(st["gt"]), g["gt"])
+    assert st["precision"] == pytest.approx(float(g["precision"]), rel=1e-12)
+    assert st["top1_error"] == pytest.approx(float(g["top1_error"]), rel=1e-12)
+    assert np.array_equal(retrieval.get_rank(g["lib"], 10), g["get_rank"])
+    ev = retrieval.retrieval_eval(g["lib"], 0.1, g["table"])
+    assert ev["mAP"] == pytest.approx(float(g["eval_mAP"]), rel=1e-9)
+    assert ev["percision"] == pytest.approx(float(g["eval_percision"]), rel=1e-12)
+    m = retrieval.compute_mAP(g["lib"], g["labels"])
+    assert m[0] == pytest.approx(float(g["mAP_instance"]), rel=1e-9)
+
+
+def test_irls_golden(ctx):
+    from corsair_b200 import _transform_estimation as te
+    g = load("irls")
+    p0, p1, w = (torch.from_numpy(g[k]) for k in ("p0", "p1", "w"))
+    for got, ref in ((te.est_quad_linear_robust(p0, p1), g["T_unweighted"]),
+                     (te.est_quad_linear_robust(p0, p1, w), g["T_weighted"])):
+        Rd = got[:3, :3].double().numpy().T @ ref[:3, :3].astype(np.float64)
+        assert np.arccos(np.clip((np.trace(Rd) - 1) / 2, -1, 1)) < 1e-4
+        assert np.linalg.norm(got[:3, 3].numpy() - ref[:3, 3]) < 1e-5
+
+
+@pytest.mark.parametrize("cat,K", [("chair", 2), ("table", 4)])
+def test_symmetric_cut4_golden(ctx, cat, K):
+    from corsair_b200 import symmetry
+    g = load("symmetry")
+    np.random.seed(31)
+    masks = np.stack(symmetry.symmetric_cut4(g[f"{cat}_F"], g[f"{cat}_xyz"], K))
+    agree = (masks == g[f"{cat}_masks"]).all(0).mean()
+    assert agree > 0.995, f"mask agreement with the reference {agree:.4f}"
+
+
+def test_sym_pose_and_ransac_golden(ctx):
+    from corsair_b200 import eval_pose, symmetry
+    g = load("symmetry")
+    np.random.seed(31)
+    Tb, cb, Tr, cr, ok = symmetry.sym_pose(g["sp_baseF"], g["sp_xyz0"], g["sp_posF"], g["sp_xyz1"], 1, k_nn=5,
+                                           max_corr=0.2, seed=31)
+    assert ok == bool(g["sp_ok"])
+    assert np.allclose(Tr.numpy(), g["sp_T_ransac"], atol=1e-5) and abs(cr - float(g["sp_ch_ransac"])) <= 1e-5 * cr
+    assert np.allclose(Tb.numpy(), g["sp_T_best"], atol=1e-5) and abs(cb - float(g["sp_ch_best"])) <= 1e-5 * cb
+    r = load("ransac_restated")
+    got = eval_pose.ransac_device(r["src"], r["tgt"], 0.2, minimal_sets=r["minimal_sets"], adaptive=False, return_all=True)
+    assert np.array_equal(got["counts"].cpu().numpy(), r["counts"])
+    assert int(got["stats"][0].item()) == int(r["best_h"])
+    np.testing.assert_allclose(got["T"].cpu().numpy(), r["T"], atol=1e-9)
+    e = eval_pose.eval_pose(torch.from_numpy(g["T_est"]), g["T0"], g["T1"], 4)
+    np.testing.assert_allclose(np.array(e), g["eval_pose_sym4"], rtol=1e-6)
