@@ -1,0 +1,89 @@
+"""Sharding helpers for one 8xB200 box (one process per GPU, torch.distributed).
+
+The path shards in three ways; only the last two exchange data, with one
+all-gather of small per-shard records:
+  * query-CAD pairs / queries: independent units, block-cyclic over ranks, no collective;
+  * retrieval: the CAD library rows are split over ranks, per-shard top-k merged by
+    (distance, global index);
+  * RANSAC hypothesis sets: ranges of the seeded hypothesis stream per rank, best records merged
+    with Open3D's rule (count desc, rmse asc, lowest hypothesis index first).
+Works with the `nccl` backend on CUDA tensors and with `gloo` on CPU tensors (CPU tests).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n, rank=None, world_size=None):
+    """Contiguous [lo, hi) share of n items for `rank` (sizes differ by at most one)."""
+    if rank is None:
+        rank, world_size = world()
+    base, rem = divmod(n, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def cyclic_items(n, rank=None, world_size=None):
+    """Block-cyclic item ids for independent units (pairs, queries)."""
+    if rank is None:
+        rank, world_size = world()
+    return list(range(rank, n, world_size))
+
+
+def _all_gather(t):
+    rank, ws = world()
+    if ws == 1:
+        return [t]
+    out = [torch.empty_like(t) for _ in range(ws)]
+    dist.all_gather(out, t.contiguous())
+    return out
+
+
+def merge_topk(idx_local, dist_local, shard_lo, k):
+    """Merge per-shard top-k lists.  idx_local [Q,k'] (indices local to the shard), dist_local
+    [Q,k'] float64 ascending; shard_lo = first global row of this rank's shard.  Every rank gets
+    the global (idx [Q,k] int64, dist [Q,k]) ordered by (distance, global index)."""
+    gi = idx_local.to(torch.int64) + int(shard_lo)
+    all_i = torch.cat(_all_gather(gi), dim=1)
+    all_d = torch.cat(_all_gather(dist_local.to(torch.float64)), dim=1)
+    # lexicographic (distance, index): stable sort by index first, then stable sort by distance
+    o1 = torch.argsort(all_i, dim=1, stable=True)
+    all_i, all_d = torch.gather(all_i, 1, o1), torch.gather(all_d, 1, o1)
+    o2 = torch.argsort(all_d, dim=1, stable=True)[:, :k]
+    return torch.gather(all_i, 1, o2), torch.gather(all_d, 1, o2)
+
+
+def merge_best_hypothesis(T, stats, h_lo):
+    """Merge per-shard RANSAC results.  T [4,4] f64, stats [4] f64 = (best_h local to the shard,
+    inliers, sum_d2, n_evaluated); h_lo = first hypothesis of this rank's range.  Returns the
+    winning (T, stats with the GLOBAL hypothesis index and the summed n_evaluated)."""
+    rec = torch.cat([T.reshape(-1).to(torch.float64), stats.to(torch.float64),
+                     torch.tensor([float(h_lo)], dtype=torch.float64, device=T.device)])
+    recs = torch.stack(_all_gather(rec)).cpu().numpy()
+    best, key = None, None
+    total_eval = 0.0
+    for r in recs:
+        h, cnt, s2, nev, lo = r[16], r[17], r[18], r[19], r[20]
+        total_eval += nev
+        if h < 0:
+            continue
+        rmse = np.sqrt(s2 / cnt) if cnt > 0 else 0.0
+        cand = (-cnt, rmse, h + lo)
+        if key is None or cand < key:
+            key, best = cand, r
+    if best is None:
+        return torch.eye(4, dtype=torch.float64, device=T.device), torch.tensor([-1.0, 0.0, 0.0, total_eval], dtype=torch.float64, device=T.device)
+    Tm = torch.tensor(best[:16].reshape(4, 4), dtype=torch.float64, device=T.device)
+    st = torch.tensor([best[16] + best[20], best[17], best[18], total_eval], dtype=torch.float64, device=T.device)
+    return Tm, st
+
+
+def gather_rows(rows):
+    """All-gather equally shaped per-rank result rows ([n_local, C]) -> [world*n_local, C]."""
+    return torch.cat(_all_gather(rows), dim=0)
