@@ -284,68 +284,127 @@ __device__ int ransac_budget_from_count(int good, int m, int n, double conf, int
     return k < (double)cap ? (int)ceil(k) : cap;
 }
 
-// one warp; folds hypotheses h0..h0+w-1 in order.
-__global__ void __launch_bounds__(32)
-ransac_fold_kernel(const int32_t* __restrict__ pc, const double* __restrict__ ps, int P, const double* __restrict__ Tw,
+// key order of Open3D's IsBetterRANSACThan plus "first hypothesis wins exact ties"
+__device__ __forceinline__ bool ransac_better(int c, double r, int h, int bc, double br, int bh) {
+    return c > bc || (c == bc && (r < br || (r == br && h < bh)));
+}
+
+// One block of 1024 threads folds hypotheses h0..h0+w-1 with the semantics of the sequential
+// scan: process h in order while h < budget; an improvement (count up, or equal count and lower
+// rmse) may shrink the budget, which depends only on the best count so far.  Parallel form:
+//   1. totals per hypothesis (sum of the P partials), written in place into row 0 of pc/ps
+//   2. block max-scan of per-segment maximum counts -> the best count BEFORE each segment
+//   3. every thread walks its contiguous segment with the running best count and finds the
+//      first h with h >= budget(best count so far); block-min -> where the scan stops
+//   4. lexicographic best over [h0, stop) merged with the best of the earlier waves.
+constexpr int kFoldThreads = 1024;
+
+__global__ void __launch_bounds__(kFoldThreads)
+ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, const double* __restrict__ Tw,
                    int h0, int w, int m, int ransac_n, int adaptive, double conf, RansacState* __restrict__ state,
                    int32_t* __restrict__ counts, double* __restrict__ sums, double* __restrict__ dev_work) {
     if (h0 >= state->budget) return;
-    const int lane = threadIdx.x;
-    if (lane == 0) dev_work[CB_T_RANSAC_SCORE] += (double)w * (double)m * 32.0;  // bytes this wave streamed
-    int budget = state->budget;
-    int best_count = state->best_count, best_h = state->best_h;
-    double best_rmse = state->best_rmse, best_sum = state->best_sum;
-    int stop = 0, n_eval = state->n_eval;
-    for (int c0 = 0; c0 < w && !stop; c0 += 32) {
-        const int j = c0 + lane;
+    __shared__ int s_scan[kFoldThreads];
+    __shared__ int s_stop;
+    __shared__ int s_wc[32], s_wh[32];
+    __shared__ double s_wr[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int budget_in = state->budget;
+    const int prev_count = state->best_count;
+    if (tid == 0) {
+        dev_work[CB_T_RANSAC_SCORE] += (double)w * (double)m * 32.0;  // bytes this wave streamed
+        s_stop = h0 + w;
+    }
+    // 1. totals (coalesced)
+    for (int j = tid; j < w; j += kFoldThreads) {
         int cnt = 0;
         double sm = 0.0;
-        if (j < w) {
-            for (int p = 0; p < P; ++p) {
-                cnt += pc[(size_t)p * w + j];
-                sm += ps[(size_t)p * w + j];
-            }
+        for (int p = 0; p < P; ++p) {
+            cnt += pc[(size_t)p * w + j];
+            sm += ps[(size_t)p * w + j];
         }
-        const double rm = cnt > 0 ? sqrt(sm / (double)cnt) : 0.0;
-        // candidates that could improve on the best known at chunk entry
-        bool cand = j < w && (cnt > best_count || (cnt == best_count && rm < best_rmse));
-        unsigned mask = __ballot_sync(0xffffffffu, cand);
-        const int valid = min(32, w - c0);
-        int processed = valid;
-        while (mask) {
-            int l = __ffs(mask) - 1;
-            mask &= mask - 1;
-            int h = h0 + c0 + l;
-            if (h >= budget) break;
-            int c = __shfl_sync(0xffffffffu, cnt, l);
-            double r = __shfl_sync(0xffffffffu, rm, l);
-            double s = __shfl_sync(0xffffffffu, sm, l);
-            if (c > best_count || (c == best_count && r < best_rmse)) {
-                best_count = c; best_rmse = r; best_sum = s; best_h = h;
-                if (lane < 12) state->T[(lane / 4) * 4 + (lane % 4)] = Tw[(size_t)(c0 + l) * 12 + lane];
-                if (adaptive) {
-                    int b = ransac_budget_from_count(c, m, ransac_n, conf, budget);
-                    if (b < budget) budget = b;
-                }
-            }
-        }
-        if (h0 + c0 + valid > budget) {
-            processed = max(0, budget - (h0 + c0));
-            stop = 1;
-        }
-        if (j < w && lane < processed) {
-            if (counts) counts[h0 + j] = cnt;
-            if (sums) sums[h0 + j] = sm;
-        }
-        n_eval = h0 + c0 + processed;
+        pc[j] = cnt;
+        ps[j] = sm;
     }
-    if (lane == 0) {
-        state->budget = budget;
-        state->best_count = best_count;
-        state->best_h = best_h;
-        state->best_rmse = best_rmse;
-        state->best_sum = best_sum;
-        state->n_eval = n_eval;
+    __syncthreads();
+    // 2. best count before each segment
+    const int L = (w + kFoldThreads - 1) / kFoldThreads;
+    const int j0 = min(w, tid * L), j1 = min(w, j0 + L);
+    int seg_max = 0;
+    for (int j = j0; j < j1; ++j) seg_max = max(seg_max, pc[j]);
+    s_scan[tid] = seg_max;
+    __syncthreads();
+    for (int off = 1; off < kFoldThreads; off <<= 1) {
+        int v = tid >= off ? s_scan[tid - off] : 0;
+        __syncthreads();
+        s_scan[tid] = max(s_scan[tid], v);
+        __syncthreads();
+    }
+    int run = max(prev_count, tid > 0 ? s_scan[tid - 1] : 0);
+    // 3. first h at or beyond the (shrinking) budget
+    if (j0 < j1) {
+        int b = adaptive ? min(budget_in, ransac_budget_from_count(run, m, ransac_n, conf, budget_in)) : budget_in;
+        int stop = -1;
+        for (int j = j0; j < j1; ++j) {
+            const int h = h0 + j;
+            if (h >= b) { stop = h; break; }
+            const int c = pc[j];
+            if (c > run) {
+                run = c;
+                if (adaptive) b = min(b, ransac_budget_from_count(run, m, ransac_n, conf, budget_in));
+            }
+        }
+        if (stop < 0 && h0 + j1 >= b && j1 < w) stop = h0 + j1;  // budget reached exactly at the segment end
+        if (stop >= 0) atomicMin(&s_stop, stop);
+    }
+    __syncthreads();
+    const int stop = s_stop;
+    // 4. best over [h0, stop)
+    int bc = -1, bh = 0x7fffffff;
+    double br = 0.0;
+    for (int j = tid; j < w && h0 + j < stop; j += kFoldThreads) {
+        const int c = pc[j];
+        const double sm = ps[j];
+        const double r = c > 0 ? sqrt(sm / (double)c) : 0.0;
+        if (counts) counts[h0 + j] = c;
+        if (sums) sums[h0 + j] = sm;
+        if (ransac_better(c, r, h0 + j, bc, br, bh)) { bc = c; br = r; bh = h0 + j; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+        double orr = __shfl_xor_sync(0xffffffffu, br, o);
+        int oh = __shfl_xor_sync(0xffffffffu, bh, o);
+        if (ransac_better(oc, orr, oh, bc, br, bh)) { bc = oc; br = orr; bh = oh; }
+    }
+    if (lane == 0) { s_wc[warp] = bc; s_wr[warp] = br; s_wh[warp] = bh; }
+    __syncthreads();
+    if (warp == 0) {
+        bc = s_wc[lane]; br = s_wr[lane]; bh = s_wh[lane];
+        for (int o = 16; o > 0; o >>= 1) {
+            int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            double orr = __shfl_xor_sync(0xffffffffu, br, o);
+            int oh = __shfl_xor_sync(0xffffffffu, bh, o);
+            if (ransac_better(oc, orr, oh, bc, br, bh)) { bc = oc; br = orr; bh = oh; }
+        }
+        // the best of the earlier waves keeps exact ties (lower hypothesis index); the default
+        // result (count 0, rmse 0) is only replaced by a hypothesis with inliers
+        const bool improve = bc >= 0 && (bc > state->best_count || (bc == state->best_count && br < state->best_rmse));
+        if (improve && lane < 12) state->T[lane] = Tw[(size_t)(bh - h0) * 12 + lane];
+        __syncwarp();
+        if (lane == 0) {
+            int best_count = state->best_count;
+            if (improve) {
+                state->best_count = bc;
+                state->best_rmse = br;
+                state->best_sum = ps[bh - h0];
+                state->best_h = bh;
+                best_count = bc;
+            }
+            int budget = budget_in;
+            if (adaptive) budget = min(budget, ransac_budget_from_count(best_count, m, ransac_n, conf, budget_in));
+            state->budget = budget;
+            state->n_eval = stop;
+        }
     }
 }
 
@@ -431,7 +490,7 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
                                                                      pc, ps);
                 CB_LAUNCH_CHECK(ctx);
             }
-            ransac_fold_kernel<<<1, 32, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
+            ransac_fold_kernel<<<1, kFoldThreads, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
                                                  counts, sums, ctx->dev_work);
             CB_LAUNCH_CHECK(ctx);
             h0 += w;

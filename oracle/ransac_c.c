@@ -175,7 +175,7 @@ int orc_ransac(const double* src, const double* tgt, int M, const int32_t* ms, i
     int32_t* gw = (int32_t*)malloc(sizeof(int32_t) * wave);
     double* sw = (double*)malloc(sizeof(double) * wave);
     double bfit = 0.0, brmse = 0.0;
-    int budget = H, h0 = 0, stop = 0;
+    int budget = H, h0 = 0, stop = 0, n_eval = -1;
     while (h0 < budget && !stop) {
         int w = wave < budget - h0 ? wave : budget - h0;
 #pragma omp parallel for schedule(dynamic, 1)
@@ -185,7 +185,7 @@ int orc_ransac(const double* src, const double* tgt, int M, const int32_t* ms, i
         }
         for (int j = 0; j < w; ++j) {
             int h = h0 + j;
-            if (h >= budget) { stop = 1; break; }
+            if (h >= budget) { stop = 1; n_eval = h; break; }
             if (counts) counts[h] = gw[j];
             if (sums) sums[h] = sw[j];
             double f = (double)gw[j] / (double)M;
@@ -208,6 +208,7 @@ int orc_ransac(const double* src, const double* tgt, int M, const int32_t* ms, i
     free(Tw);
     free(gw);
     free(sw);
+    if (n_eval >= 0) return n_eval; /* first hypothesis index at or beyond the budget */
     return h0 < budget ? h0 : budget;
 }
 
