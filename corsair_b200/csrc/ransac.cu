@@ -8,10 +8,10 @@
 // beyond the device-side budget exits immediately):
 //   fit    one thread per hypothesis: gather the minimal set (explicit, or the counter-based
 //          seeded draw), Umeyama without scale in float64 with a one-sided Jacobi 3x3 SVD
-//   score  block = 128 hypotheses (one per thread, pose in registers) x a slice of the
-//          correspondences streamed through shared memory as float4 pairs; fp32 evaluation,
-//          float64 unfused re-evaluation inside the rounding band around max_dist^2 so the
-//          inlier COUNT is exactly the float64 one
+//   score  block = 512 hypotheses (four per thread as two register pairs, FFMA2/FADD2 packed
+//          fp32) x a slice of the correspondences streamed through shared memory; float64
+//          unfused re-evaluation inside the rounding band around max_dist^2 so the inlier COUNT
+//          is exactly the float64 one
 //   fold   one warp folds the wave in hypothesis order with Open3D's "better" rule
 //          (count desc, rmse asc, first wins ties) and its adaptive budget update.
 #include "common.cuh"
@@ -207,71 +207,166 @@ __global__ void ransac_draw_kernel(uint64_t seed, int m, size_t total, int32_t* 
 }
 
 // ------------------------------------------------------------------------- score
-// grid (ceil(w/128), P); block 128.  Thread = hypothesis, points streamed through smem.
+// Packed-fp32 scoring.  Block = 128 threads, each thread owns 2*NP hypotheses held as NP register
+// PAIRS (h, h+1) so every arithmetic instruction is an FFMA2/FADD2 over two hypotheses; a slice of
+// the correspondences is streamed through shared memory with every coordinate stored twice
+// ((x,x),(y,y),...) so one LDS.128 yields two ready-made operand pairs, broadcast to the warp.
+// Per (hypothesis, correspondence): e = R s + (t - q), d2 = |e|^2, u = d2 - thr^2;
+// inlier mask = (u < 0) as 1.0f/0.0f feeding packed count/sum accumulators.  When |u| falls inside
+// the fp32 rounding band the oracle's unfused float64 expression decides instead, so the COUNT is
+// exactly the float64 count.  grid (ceil(w / (256*NP)), P).
 constexpr int kScoreTile = 256;
+typedef unsigned long long f32x2;
 
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// the oracle's float64 evaluation (unfused, same association order) of one pair
+__device__ __noinline__ double ransac_exact_d2(const double* __restrict__ Td, float4 s, float4 q) {
+    const double x = s.x, y = s.y, z = s.z;
+    double f0 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[0], x), __dmul_rn(Td[1], y)), __dmul_rn(Td[2], z)), Td[3]), (double)q.x);
+    double f1 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[4], x), __dmul_rn(Td[5], y)), __dmul_rn(Td[6], z)), Td[7]), (double)q.y);
+    double f2 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[8], x), __dmul_rn(Td[9], y)), __dmul_rn(Td[10], z)), Td[11]), (double)q.z);
+    return __dadd_rn(__dadd_rn(__dmul_rn(f0, f0), __dmul_rn(f1, f1)), __dmul_rn(f2, f2));
+}
+
+template <int NP>
 __global__ void __launch_bounds__(128)
 ransac_score_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int split,
                     const double* __restrict__ Tw, int h0, int w, double thr2d,
                     const RansacState* __restrict__ state, int32_t* __restrict__ pc, double* __restrict__ ps) {
     if (h0 >= state->budget) return;
-    __shared__ float4 ss[kScoreTile];
-    __shared__ float4 st[kScoreTile];
-    const int j = blockIdx.x * 128 + threadIdx.x;
-    const int jj = min(j, w - 1);
-    const double* Td = Tw + (size_t)jj * 12;
-    const float r00 = (float)Td[0], r01 = (float)Td[1], r02 = (float)Td[2], t0 = (float)Td[3];
-    const float r10 = (float)Td[4], r11 = (float)Td[5], r12 = (float)Td[6], t1 = (float)Td[7];
-    const float r20 = (float)Td[8], r21 = (float)Td[9], r22 = (float)Td[10], t2 = (float)Td[11];
-    // rounding band of the fp32 evaluation around thr^2 (see DESIGN.md, "RANSAC exactness")
+    __shared__ float4 sp[kScoreTile * 3];  // per point: (x,x,y,y) (z,z,-qx,-qx) (-qy,-qy,-qz,-qz)
+    const int jbase = (blockIdx.x * 128 + threadIdx.x) * 2 * NP;  // first hypothesis of this thread
+    f32x2 R[NP][9], Tt[NP][3];
+    float tn_max = 0.f;
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+        const double* Ta = Tw + (size_t)min(jbase + 2 * p, w - 1) * 12;
+        const double* Tb = Tw + (size_t)min(jbase + 2 * p + 1, w - 1) * 12;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) R[p][3 * r + c] = pk2((float)Ta[4 * r + c], (float)Tb[4 * r + c]);
+            Tt[p][r] = pk2((float)Ta[4 * r + 3], (float)Tb[4 * r + 3]);
+        }
+        float ta = sqrtf((float)(Ta[3] * Ta[3] + Ta[7] * Ta[7] + Ta[11] * Ta[11]));
+        float tb = sqrtf((float)(Tb[3] * Tb[3] + Tb[7] * Tb[7] + Tb[11] * Tb[11]));
+        tn_max = fmaxf(tn_max, fmaxf(ta, tb));
+    }
+    // rounding band of the fp32 evaluation around thr^2 (DESIGN.md, "RANSAC exactness")
     const float smax = __uint_as_float(state->smax_bits), tmax = __uint_as_float(state->tmax_bits);
-    const float tn = sqrtf(t0 * t0 + t1 * t1 + t2 * t2);
-    const float errv = 16.f * 5.9604645e-8f * (smax + tmax + tn);
+    const float errv = 16.f * 5.9604645e-8f * (smax + tmax + tn_max);
     const float thr2 = (float)thr2d;
     const float band = 2.f * sqrtf(thr2) * errv + errv * errv + 8.f * 5.9604645e-8f * thr2;
-    const float lo = thr2 - band, hi = thr2 + band;
+    const f32x2 nthr2 = pk2(-thr2, -thr2);
+    const f32x2 zero2 = pk2(0.f, 0.f);
 
     const int p0 = blockIdx.y * split, p1 = min(m, p0 + split);
-    int count = 0;
-    double sum = 0.0;
+    int cnt[2 * NP];
+    double sum[2 * NP];
+#pragma unroll
+    for (int e = 0; e < 2 * NP; ++e) { cnt[e] = 0; sum[e] = 0.0; }
+
     for (int base = p0; base < p1; base += kScoreTile) {
         const int nt = min(kScoreTile, p1 - base);
         __syncthreads();
         for (int t = threadIdx.x; t < nt; t += 128) {
-            ss[t] = src4[base + t];
-            st[t] = tgt4[base + t];
+            const float4 s = src4[base + t], q = tgt4[base + t];
+            sp[3 * t] = make_float4(s.x, s.x, s.y, s.y);
+            sp[3 * t + 1] = make_float4(s.z, s.z, -q.x, -q.x);
+            sp[3 * t + 2] = make_float4(-q.y, -q.y, -q.z, -q.z);
         }
         __syncthreads();
-        float fsum = 0.f;
-#pragma unroll 4
+        f32x2 fc[NP], fs[NP];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) { fc[p] = zero2; fs[p] = zero2; }
+#pragma unroll 2
         for (int t = 0; t < nt; ++t) {
-            const float4 s = ss[t];
-            const float4 q = st[t];
-            float e0 = fmaf(r00, s.x, fmaf(r01, s.y, fmaf(r02, s.z, t0 - q.x)));
-            float e1 = fmaf(r10, s.x, fmaf(r11, s.y, fmaf(r12, s.z, t1 - q.y)));
-            float e2 = fmaf(r20, s.x, fmaf(r21, s.y, fmaf(r22, s.z, t2 - q.z)));
-            float d2 = fmaf(e2, e2, fmaf(e1, e1, e0 * e0));
-            if (d2 < hi) {
-                if (d2 >= lo) {
-                    // inside the band: the oracle's float64 expression, unfused, same order
-                    double x = s.x, y = s.y, z = s.z;
-                    double f0 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[0], x), __dmul_rn(Td[1], y)), __dmul_rn(Td[2], z)), Td[3]), (double)q.x);
-                    double f1 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[4], x), __dmul_rn(Td[5], y)), __dmul_rn(Td[6], z)), Td[7]), (double)q.y);
-                    double f2 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[8], x), __dmul_rn(Td[9], y)), __dmul_rn(Td[10], z)), Td[11]), (double)q.z);
-                    double dd = __dadd_rn(__dadd_rn(__dmul_rn(f0, f0), __dmul_rn(f1, f1)), __dmul_rn(f2, f2));
-                    if (dd < thr2d) { ++count; fsum += (float)dd; }
-                } else {
-                    ++count;
-                    fsum += d2;
+            const ulonglong2 v0 = *reinterpret_cast<const ulonglong2*>(&sp[3 * t]);
+            const ulonglong2 v1 = *reinterpret_cast<const ulonglong2*>(&sp[3 * t + 1]);
+            const ulonglong2 v2 = *reinterpret_cast<const ulonglong2*>(&sp[3 * t + 2]);
+            const f32x2 X = v0.x, Y = v0.y, Z = v1.x, NQX = v1.y, NQY = v2.x, NQZ = v2.y;
+            f32x2 d2[NP];
+            float mlo[NP], mhi[NP];
+            float bmin = INFINITY;
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                f32x2 e0 = fma2(R[p][0], X, fma2(R[p][1], Y, fma2(R[p][2], Z, add2(Tt[p][0], NQX))));
+                f32x2 e1 = fma2(R[p][3], X, fma2(R[p][4], Y, fma2(R[p][5], Z, add2(Tt[p][1], NQY))));
+                f32x2 e2 = fma2(R[p][6], X, fma2(R[p][7], Y, fma2(R[p][8], Z, add2(Tt[p][2], NQZ))));
+                d2[p] = fma2(e2, e2, fma2(e1, e1, mul2(e0, e0)));
+                float ulo, uhi;
+                unpk2(add2(d2[p], nthr2), ulo, uhi);
+                mlo[p] = ulo < 0.f ? 1.f : 0.f;
+                mhi[p] = uhi < 0.f ? 1.f : 0.f;
+                bmin = fminf(bmin, fminf(fabsf(ulo), fabsf(uhi)));
+            }
+            if (bmin <= band) {
+                // some evaluation of this thread sits inside the band: float64 decides for those
+                const float4 s = src4[base + t], q = tgt4[base + t];
+#pragma unroll
+                for (int p = 0; p < NP; ++p) {
+                    float dlo, dhi;
+                    unpk2(d2[p], dlo, dhi);
+                    if (fabsf(dlo - thr2) <= band) {
+                        double dd = ransac_exact_d2(Tw + (size_t)min(jbase + 2 * p, w - 1) * 12, s, q);
+                        mlo[p] = dd < thr2d ? 1.f : 0.f;
+                        dlo = (float)dd;
+                    }
+                    if (fabsf(dhi - thr2) <= band) {
+                        double dd = ransac_exact_d2(Tw + (size_t)min(jbase + 2 * p + 1, w - 1) * 12, s, q);
+                        mhi[p] = dd < thr2d ? 1.f : 0.f;
+                        dhi = (float)dd;
+                    }
+                    d2[p] = pk2(dlo, dhi);
                 }
             }
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const f32x2 mk = pk2(mlo[p], mhi[p]);
+                fc[p] = add2(fc[p], mk);
+                fs[p] = fma2(mk, d2[p], fs[p]);
+            }
         }
-        sum += (double)fsum;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+            float a, b2;
+            unpk2(fc[p], a, b2);
+            cnt[2 * p] += (int)a;
+            cnt[2 * p + 1] += (int)b2;
+            unpk2(fs[p], a, b2);
+            sum[2 * p] += (double)a;
+            sum[2 * p + 1] += (double)b2;
+        }
     }
-    if (j < w) {
-        pc[(size_t)blockIdx.y * w + j] = count;
-        ps[(size_t)blockIdx.y * w + j] = sum;
-    }
+#pragma unroll
+    for (int e = 0; e < 2 * NP; ++e)
+        if (jbase + e < w) {
+            pc[(size_t)blockIdx.y * w + jbase + e] = cnt[e];
+            ps[(size_t)blockIdx.y * w + jbase + e] = sum[e];
+        }
 }
 
 // -------------------------------------------------------------------------- fold
@@ -447,10 +542,10 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
     (void)n_src;
     (void)n_tgt;
     const int wmax = 32768;
-    const int P_max = 64;
+    const size_t pw_max = size_t(1) << 20;  // entries of the [P, w] partial count / sum arrays
+    constexpr int NP = 2;                   // hypothesis pairs per scoring thread
     size_t need = cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) +
-                  cb_align((size_t)wmax * 12 * 8) + cb_align((size_t)P_max * wmax * 4) +
-                  cb_align((size_t)P_max * wmax * 8);
+                  cb_align((size_t)wmax * 12 * 8) + cb_align(pw_max * 4) + cb_align(pw_max * 8);
     if ((rc = cb_reserve(ctx, need))) return rc;
     RansacState* state = cb_alloc_t<RansacState>(ctx, 1);
     if (!state) return CB_ENOMEM;
@@ -463,8 +558,8 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         float4* src4 = cb_alloc_t<float4>(ctx, m);
         float4* tgt4 = cb_alloc_t<float4>(ctx, m);
         double* Tw = cb_alloc_t<double>(ctx, (size_t)wmax * 12);
-        int32_t* pc = cb_alloc_t<int32_t>(ctx, (size_t)P_max * wmax);
-        double* ps = cb_alloc_t<double>(ctx, (size_t)P_max * wmax);
+        int32_t* pc = cb_alloc_t<int32_t>(ctx, pw_max);
+        double* ps = cb_alloc_t<double>(ctx, pw_max);
         if (!src4 || !tgt4 || !Tw || !pc || !ps) return CB_ENOMEM;
         ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, src_idx, tgt_idx, m, src4, tgt4,
                                                               state);
@@ -473,9 +568,9 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         int h0 = 0;
         for (int wave = 0; h0 < h_total; ++wave) {
             const int w = min(ransac_wave_size(wave), h_total - h0);
-            const int groups = cb_div_up(w, 128);
-            int P = cb_div_up(3 * ctx->sm_count, groups);
-            P = max(1, min(min(P, P_max), cb_div_up(m, kScoreTile)));
+            const int groups = cb_div_up(w, 128 * 2 * NP);
+            int P = cb_div_up(8 * ctx->sm_count, groups);  // ~2 waves at 4 resident blocks per SM
+            P = max(1, min(min(P, (int)(pw_max / (size_t)w)), cb_div_up(m, kScoreTile)));
             int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
             P = cb_div_up(m, split);
             {
@@ -486,7 +581,7 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
             }
             {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
-                ransac_score_kernel<<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state,
+                ransac_score_kernel<NP><<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state,
                                                                      pc, ps);
                 CB_LAUNCH_CHECK(ctx);
             }
