@@ -300,7 +300,7 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     S = max(1, min(S, 128 / KC));
     S = min(S, max(1, nr / 256));
     int chunk = cb_div_up(nr, S);
-    chunk = (chunk + 127) & ~127;  // whole tensor-core column tiles per chunk
+    chunk = (chunk + 255) & ~255;  // whole tensor-core column tiles (256 references) per chunk
     S = cb_div_up(nr, chunk);
 
     const float* qd = q;
@@ -364,7 +364,7 @@ static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
     b += cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nr * 32 * 4);  // pads
     b += cb_align((size_t)nr * 4) + 256;
     b += 2 * cb_align((size_t)nq * 128 * 4) + cb_align((size_t)nq * 4);
-    b += cb_align((size_t)(nq + nr) * 32 * 2 * 2) + (1 << 16);  // bf16 hi/lo operands of the tc variant
+    b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + (1 << 16);  // packed bf16 operand tiles of the tc variant
     return b;
 }
 

@@ -1,10 +1,246 @@
-// tcgen05 candidate pass of the kNN engine (placeholder until the tensor-core kernel lands).
+// tcgen05 candidate pass of the kNN engine (K1): the distance GEMM on the 5th-generation tensor
+// cores in split precision, fused with the running top-KC of every query row.
+//
+// Split-bf16 ("bf16x3"): q = qh + ql, r = rh + rl (bf16 each);  q.r ~= qh.rh + qh.rl + ql.rh.
+// The three products are ONE GEMM over a widened K axis:
+//     A row (query)     [ qh (D) | qh (D) | ql (D) | 1 1 1 0 ... (16) ]
+//     B row (reference) [ rh (D) | rl (D) | rh (D) | c0 c1 c2 0 ... (16) ],  c0+c1+c2 = -|r|^2/2
+// so the accumulator is dot' = q.r - |r|^2/2 and the squared distance ordering is simply
+// "largest dot' first" (score s = -2 dot' = |r|^2 - 2 q.r, the candidate-list convention of
+// knn.cu).  Error: |dot' - exact| <= 3*2^-18 |q||r| + fp32 accumulation, covered by
+// knn_cand_tc_gamma() in the re-rank's proof obligation.
+//
+// Pipeline per CTA (one 128-query tile x one reference chunk), 192 threads:
+//   warp 4  producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
+//   warp 5  one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
+//           of two 256-column TMEM accumulators and commits to mbarriers
+//   warps 0-3 epilogue: tcgen05.ld 32 columns at a time, group-max filter against the row's
+//           current KC-th best, sorted insertion in registers; overlaps the next tile's MMAs.
 #include "common.cuh"
 #include "knn_internal.cuh"
+#include "tc_common.cuh"
 
-int knn_cand_tc_launch(cb_ctx*, const float*, int, const float*, const float*, int, int, int, int, int, int,
-                       int32_t*, float*, cudaStream_t) {
-    return CB_EUNSUPPORTED;
+#include <math.h>
+
+namespace {
+
+constexpr int kTileM = 128;   // queries per CTA (TMEM lanes)
+constexpr int kTileN = 256;   // references per MMA / accumulator stage
+constexpr int kExtraK = 16;   // the norm block of the widened K axis
+constexpr int kThreads = 192;
+
+__host__ __device__ constexpr int kprime(int D) { return 3 * D + kExtraK; }
+
+// fp32 rows [n, D] -> packed bf16 operand tiles.  One thread per (row, 8-column group).
+// is_b: 0 = A layout (hi|hi|lo|ones), 1 = B layout (hi|lo|hi|-norm/2 split in three).
+__global__ void knn_tc_pack_kernel(const float* __restrict__ x, const float* __restrict__ norms, int n, int n_pad,
+                                   int D, int TR, int is_b, int maxdot, __nv_bfloat16* __restrict__ out) {
+    const int KP = kprime(D);
+    const int groups = KP / 8;
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (size_t)n_pad * groups) return;
+    const int row = (int)(gid / groups), kc = (int)(gid % groups);
+    __nv_bfloat16 v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = __float2bfloat16_rn(0.f);
+    const int k0 = kc * 8;
+    if (k0 < 3 * D) {
+        if (row < n) {
+            const int part = k0 / D;          // 0,1,2
+            const int c0 = k0 - part * D;     // column inside the part
+            const bool want_lo = is_b ? (part == 1) : (part == 2);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                __nv_bfloat16 hi, lo;
+                tc::split2(x[(size_t)row * D + c0 + e], hi, lo);
+                v[e] = want_lo ? lo : hi;
+            }
+        }
+    } else if (k0 == 3 * D) {
+        if (!is_b) {
+            if (row < n) { v[0] = v[1] = v[2] = __float2bfloat16_rn(1.f); }
+        } else if (row < n) {
+            if (!maxdot) tc::split3(-0.5f * norms[row], v[0], v[1], v[2]);
+        } else {
+            v[0] = __float2bfloat16_rn(-1e30f);  // padding references can never enter a list
+        }
+    }
+    const int tile = row / TR, r = row % TR;
+    char* dst = reinterpret_cast<char*>(out) + (size_t)tile * TR * KP * 2 + tc::tile_offset(TR, r, kc);
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
 }
-double knn_cand_tc_gamma(int) { return 0.0; }
-extern "C" const char* cb_knn_variant(const cb_ctx* ctx) { return "simt"; }
+
+struct TcSmemCtl {
+    uint64_t a_full, full[2], empty[2], tmem_full[2], tmem_empty[2];
+    uint32_t tmem_base;
+};
+
+template <int D, int KC>
+__global__ void __launch_bounds__(kThreads, 1)
+knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack, int nq, int nr,
+              int chunk, int S, int maxdot, int32_t* __restrict__ cand_idx, float* __restrict__ cand_s) {
+    constexpr int KP = kprime(D);
+    constexpr uint32_t A_BYTES = kTileM * KP * 2, B_BYTES = kTileN * KP * 2;
+    constexpr uint32_t LBO_A = (kTileM / 8) * 128, LBO_B = (kTileN / 8) * 128;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    unsigned char* sA = smem;
+    unsigned char* sB = smem + A_BYTES;
+    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + 2 * B_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = blockIdx.y;
+    const int t0 = (c * chunk) / kTileN;
+    const int t1 = min((nr + kTileN - 1) / kTileN, ((c + 1) * chunk) / kTileN);
+    const int ntiles = t1 - t0;
+
+    if (threadIdx.x == 0) {
+        tc::mbar_init(&ctl->a_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(&ctl->full[i], 1);
+            tc::mbar_init(&ctl->empty[i], 1);
+            tc::mbar_init(&ctl->tmem_full[i], 1);
+            tc::mbar_init(&ctl->tmem_empty[i], 4);
+        }
+        tc::fence_barrier_init();
+    }
+    if (warp == 4) tc::tmem_alloc(&ctl->tmem_base, 512);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tbase = ctl->tmem_base;
+
+    if (warp == 4) {
+        // ===== producer: bulk copies of pre-packed tiles =====
+        if (lane == 0) {
+            tc::mbar_arrive_expect_tx(&ctl->a_full, A_BYTES);
+            tc::bulk_g2s(sA, reinterpret_cast<const char*>(Apack) + (size_t)blockIdx.x * A_BYTES, A_BYTES, &ctl->a_full);
+            for (int it = 0; it < ntiles; ++it) {
+                const int st = it & 1, use = it >> 1;
+                tc::mbar_wait(&ctl->empty[st], (use & 1) ^ 1);
+                tc::mbar_arrive_expect_tx(&ctl->full[st], B_BYTES);
+                tc::bulk_g2s(sB + st * B_BYTES, reinterpret_cast<const char*>(Bpack) + (size_t)(t0 + it) * B_BYTES, B_BYTES,
+                             &ctl->full[st]);
+            }
+        }
+    } else if (warp == 5) {
+        // ===== MMA issuer: one thread =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::idesc_bf16(kTileM, kTileN);
+            const uint32_t a_addr = tc::smem_u32(sA);
+            tc::mbar_wait(&ctl->a_full, 0);
+            for (int it = 0; it < ntiles; ++it) {
+                const int st = it & 1, use = it >> 1;
+                tc::mbar_wait(&ctl->full[st], use & 1);
+                tc::mbar_wait(&ctl->tmem_empty[st], (use & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t b_addr = tc::smem_u32(sB + st * B_BYTES);
+#pragma unroll
+                for (int ks = 0; ks < KP / 16; ++ks) {
+                    const uint64_t ad = tc::smem_desc(a_addr + ks * 2 * LBO_A, LBO_A, 128);
+                    const uint64_t bd = tc::smem_desc(b_addr + ks * 2 * LBO_B, LBO_B, 128);
+                    tc::mma_bf16(tbase + st * kTileN, ad, bd, idesc, ks > 0);
+                }
+                tc::mma_commit(&ctl->empty[st]);      // smem stage reusable once these MMAs finish
+                tc::mma_commit(&ctl->tmem_full[st]);  // accumulator ready for the epilogue
+            }
+        }
+    } else {
+        // ===== epilogue: 128 threads, one query row (TMEM lane) each =====
+        const int row = threadIdx.x;
+        const int qi = blockIdx.x * kTileM + row;
+        float bs[KC];
+        int bi[KC];
+#pragma unroll
+        for (int t = 0; t < KC; ++t) { bs[t] = -INFINITY; bi[t] = -1; }
+        for (int it = 0; it < ntiles; ++it) {
+            const int st = it & 1, use = it >> 1;
+            tc::mbar_wait(&ctl->tmem_full[st], use & 1);
+            tc::fence_after_sync();
+            const int col0 = (t0 + it) * kTileN;
+#pragma unroll 1
+            for (int cb = 0; cb < kTileN / 32; ++cb) {
+                float v[32];
+                tc::tmem_ld32(tbase + ((uint32_t)(warp * 32) << 16) + st * kTileN + cb * 32, v);
+                tc::tmem_ld_wait();
+                float g = v[0];
+#pragma unroll
+                for (int e = 1; e < 32; ++e) g = fmaxf(g, v[e]);
+                if (g > bs[KC - 1]) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        if (v[e] > bs[KC - 1]) {
+                            bs[KC - 1] = v[e];
+                            bi[KC - 1] = col0 + cb * 32 + e;
+#pragma unroll
+                            for (int t = KC - 1; t > 0; --t) {
+                                if (bs[t] > bs[t - 1]) {
+                                    float fs = bs[t]; bs[t] = bs[t - 1]; bs[t - 1] = fs;
+                                    int fi = bi[t]; bi[t] = bi[t - 1]; bi[t - 1] = fi;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
+        }
+        if (qi < nq) {
+            const size_t o = ((size_t)qi * S + c) * KC;
+#pragma unroll
+            for (int t = 0; t < KC; ++t) {
+                const bool ok = bi[t] >= 0 && bi[t] < nr;
+                cand_idx[o + t] = ok ? bi[t] : -1;
+                cand_s[o + t] = ok ? (maxdot ? -bs[t] : -2.f * bs[t]) : INFINITY;
+            }
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 4) tc::tmem_dealloc(tbase, 512);
+}
+
+template <int D, int KC>
+cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
+                      int32_t* ci, float* cs, cudaStream_t st) {
+    constexpr int KP = kprime(D);
+    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + sizeof(TcSmemCtl) + 64;
+    cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    dim3 grid((nq + kTileM - 1) / kTileM, S);
+    knn_tc_kernel<D, KC><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, ci, cs);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+double knn_cand_tc_gamma(int) { return 1.5e-5; }
+
+extern "C" const char* cb_knn_variant(const cb_ctx* ctx) {
+    return (ctx && ctx->knn_variant == 1) ? "simt" : "tcgen05";
+}
+
+int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr, int d, int KC,
+                       int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s, cudaStream_t st) {
+    if ((d != 16 && d != 32) || (KC != 8 && KC != 16) || chunk % kTileN != 0) return CB_EUNSUPPORTED;
+    const int KP = kprime(d);
+    const int nq_pad = cb_div_up(nq, kTileM) * kTileM, nr_pad = cb_div_up(nr, kTileN) * kTileN;
+    __nv_bfloat16* A = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nq_pad * KP);
+    __nv_bfloat16* B = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nr_pad * KP);
+    if (!A || !B) return CB_ENOMEM;
+    const int groups = KP / 8;
+    knn_tc_pack_kernel<<<(unsigned)(((size_t)nq_pad * groups + 255) / 256), 256, 0, st>>>(q, nullptr, nq, nq_pad, d,
+                                                                                          kTileM, 0, maxdot, A);
+    CB_LAUNCH_CHECK(ctx);
+    knn_tc_pack_kernel<<<(unsigned)(((size_t)nr_pad * groups + 255) / 256), 256, 0, st>>>(r, rn, nr, nr_pad, d, kTileN, 1,
+                                                                                          maxdot, B);
+    CB_LAUNCH_CHECK(ctx);
+    cudaError_t e;
+    if (d == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
+    else if (d == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
+    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
+    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
+    ctx->launches++;
+    if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "knn_tc_kernel launch failed: %s", cudaGetErrorString(e));
+    return CB_OK;
+}
