@@ -29,6 +29,7 @@ SIGNATURES = {
     "cb_launch_count": (ctypes.c_int64, [c_void_p]),
     "cb_knn_variant": (ctypes.c_char_p, [c_void_p]),
     "cb_set_knn_variant": (c_int, [c_void_p, c_int]),
+    "cb_knn_last_fallback_rows": (c_int, [c_void_p, c_void_p]),
     "cb_timing_enable": (c_int, [c_void_p, c_int]),
     "cb_timing_read": (c_int, [c_void_p, c_int, ctypes.POINTER(c_double), ctypes.POINTER(c_double),
                                ctypes.POINTER(ctypes.c_int64)]),
@@ -132,6 +133,9 @@ class Context:
 
     def set_knn_variant(self, v):
         self.lib.cb_set_knn_variant(self.handle, int(v))
+
+    def knn_last_fallback_rows(self, stream=0):
+        return int(self.lib.cb_knn_last_fallback_rows(self.handle, c_void_p(stream)))
 
     TIMING_CLASSES = ("knn_candidates", "knn_rerank", "ransac_score", "ransac_fit", "chamfer_nn",
                       "rows_select", "kmeans")

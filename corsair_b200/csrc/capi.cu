@@ -77,6 +77,7 @@ int cb_reserve(cb_ctx* ctx, size_t bytes) {
     CB_CUDA(ctx, cudaDeviceSynchronize());
     if (ctx->arena) cudaFree(ctx->arena);
     ctx->arena = nullptr;
+    ctx->knn_fb_count = nullptr;
     ctx->arena_bytes = 0;
     size_t want = bytes + bytes / 4;
     if (cudaMalloc(&ctx->arena, want) != cudaSuccess) {

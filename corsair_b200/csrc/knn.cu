@@ -323,6 +323,7 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     int32_t* fb = cb_alloc_t<int32_t>(ctx, nq);
     if (!rn || !scal || !ci || !cs || !fb) return CB_ENOMEM;
     CB_CUDA(ctx, cudaMemsetAsync(scal, 0, 2 * sizeof(unsigned int), st));
+    ctx->knn_fb_count = (const int*)(scal + 1);
     knn_norms_kernel<<<cb_div_up(nr, 256), 256, 0, st>>>(rd, nr, dp, rn, scal);
     CB_LAUNCH_CHECK(ctx);
 
@@ -395,6 +396,14 @@ extern "C" int cb_knn(cb_ctx* ctx, const float* q, int nq, const float* r, int n
         CB_LAUNCH_CHECK(ctx);
     }
     return CB_OK;
+}
+
+extern "C" int cb_knn_last_fallback_rows(cb_ctx* ctx, void* stream) {
+    if (!ctx || !ctx->knn_fb_count) return -1;
+    int n = -1;
+    if (cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) return -1;
+    if (cudaMemcpy(&n, ctx->knn_fb_count, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return n;
 }
 
 extern "C" int cb_knn_ragged(cb_ctx* ctx, const float* q, const float* r, int d, int k, int metric,

@@ -58,6 +58,10 @@ int64_t cb_launch_count(const cb_ctx* ctx);
 const char* cb_knn_variant(const cb_ctx* ctx);
 /* force a kNN candidate variant (0 = auto, 1 = simt fp32, 2 = tcgen05 bf16x3); for tests/bench */
 int cb_set_knn_variant(cb_ctx* ctx, int variant);
+/* diagnostic: rows of the most recent E1 kNN problem of this ctx that failed the re-rank's proof
+ * obligation and were recomputed by the exact brute-force kernel (synchronises the stream);
+ * -1 if no E1 problem has run since the last arena growth */
+int cb_knn_last_fallback_rows(cb_ctx* ctx, void* stream);
 
 /* ---- instrumentation for bench.py ---------------------------------------------------------
  * With timing enabled every launch of a tracked kernel class is bracketed by CUDA events on the
