@@ -29,6 +29,9 @@ SIGNATURES = {
     "cb_launch_count": (ctypes.c_int64, [c_void_p]),
     "cb_knn_variant": (ctypes.c_char_p, [c_void_p]),
     "cb_set_knn_variant": (c_int, [c_void_p, c_int]),
+    "cb_ransac_variant": (ctypes.c_char_p, [c_void_p]),
+    "cb_set_ransac_variant": (c_int, [c_void_p, c_int]),
+    "cb_ransac_debug_dump": (c_int, [c_void_p, c_void_p, c_int]),
     "cb_knn_last_fallback_rows": (c_int, [c_void_p, c_void_p]),
     "cb_timing_enable": (c_int, [c_void_p, c_int]),
     "cb_timing_read": (c_int, [c_void_p, c_int, ctypes.POINTER(c_double), ctypes.POINTER(c_double),
@@ -133,6 +136,19 @@ class Context:
 
     def set_knn_variant(self, v):
         self.lib.cb_set_knn_variant(self.handle, int(v))
+
+    def ransac_variant(self):
+        return self.lib.cb_ransac_variant(self.handle).decode()
+
+    def set_ransac_variant(self, v):
+        self.lib.cb_set_ransac_variant(self.handle, int(v))
+
+    def ransac_debug_dump(self, tensor=None):
+        """Route the raw tensor-core values of the next cb_ransac calls into `tensor` [H, ld] f32."""
+        if tensor is None:
+            self.lib.cb_ransac_debug_dump(self.handle, None, 0)
+        else:
+            self.lib.cb_ransac_debug_dump(self.handle, c_void_p(tensor.data_ptr()), int(tensor.shape[1]))
 
     def knn_last_fallback_rows(self, stream=0):
         return int(self.lib.cb_knn_last_fallback_rows(self.handle, c_void_p(stream)))

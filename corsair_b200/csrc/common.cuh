@@ -17,6 +17,9 @@ struct cb_ctx {
     size_t arena_off = 0;       // bump pointer, reset at the start of every public call
     int64_t launches = 0;
     int knn_variant = 0;        // 0 auto, 1 simt, 2 tcgen05
+    int ransac_variant = 0;     // 0 auto (tcgen05), 1 simt fp32, 2 tcgen05
+    float* ransac_dump = nullptr;  // test hook: the tensor-core values U[h, c] of the next cb_ransac
+    int ransac_dump_ld = 0;
     const int* knn_fb_count = nullptr;  // device counter of the last E1 kNN problem (diagnostic)
     char err[512] = {0};
     // bench instrumentation (cb_timing_*): CUDA-event brackets around the tracked kernel classes

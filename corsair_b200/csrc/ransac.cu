@@ -14,21 +14,9 @@
 //          is exactly the float64 one
 //   fold   one warp folds the wave in hypothesis order with Open3D's "better" rule
 //          (count desc, rmse asc, first wins ties) and its adaptive budget update.
-#include "common.cuh"
+#include "ransac_internal.cuh"
 
 #include <math.h>
-
-struct RansacState {
-    int budget;       // hypotheses to evaluate in total (shrinks when adaptive)
-    int best_h;
-    int best_count;
-    int n_eval;
-    double best_sum;
-    double best_rmse;
-    double T[16];
-    unsigned int smax_bits;  // max |src| (fp32 bits), max |tgt|
-    unsigned int tmax_bits;
-};
 
 // -------------------------------------------------------------------------- pack
 __global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const float* __restrict__ tgt_xyz,
@@ -37,6 +25,7 @@ __global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const floa
                                    RansacState* __restrict__ state) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     float ns = 0.f, nt = 0.f;
+    float4 sv = make_float4(0.f, 0.f, 0.f, 0.f), tv = sv;
     if (i < m) {
         size_t a = src_idx ? (size_t)src_idx[i] : (size_t)i;
         size_t b = tgt_idx ? (size_t)tgt_idx[i] : (size_t)i;
@@ -44,6 +33,8 @@ __global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const floa
         float4 t = make_float4(tgt_xyz[3 * b], tgt_xyz[3 * b + 1], tgt_xyz[3 * b + 2], 0.f);
         src4[i] = s;
         tgt4[i] = t;
+        sv = s;
+        tv = t;
         ns = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z);
         nt = sqrtf(t.x * t.x + t.y * t.y + t.z * t.z);
     }
@@ -54,6 +45,21 @@ __global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const floa
     if ((threadIdx.x & 31) == 0) {
         if (ns > 0.f) atomicMax(&state->smax_bits, __float_as_uint(ns));
         if (nt > 0.f) atomicMax(&state->tmax_bits, __float_as_uint(nt));
+    }
+    // correspondence means for the tensor-core features (any centre is valid: it only tightens
+    // the rounding band, the decisions inside the band are re-made exactly)
+    double acc[6] = {(double)sv.x, (double)sv.y, (double)sv.z, (double)tv.x, (double)tv.y, (double)tv.z};
+    __shared__ double s_acc[8][6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+        for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+        if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5][c] = acc[c];
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double t = 0.0;
+        for (int wv = 0; wv < (int)(blockDim.x >> 5); ++wv) t += s_acc[wv][threadIdx.x];
+        atomicAdd(&state->csum[threadIdx.x], t);
     }
 }
 
@@ -68,6 +74,10 @@ __global__ void ransac_init_kernel(RansacState* state, int h_total) {
         for (int i = 0; i < 16; ++i) state->T[i] = (i % 5 == 0) ? 1.0 : 0.0;
         state->smax_bits = 0;
         state->tmax_bits = 0;
+        for (int i = 0; i < 6; ++i) state->csum[i] = 0.0;
+        state->smaxc_bits = 0;
+        state->tmaxc_bits = 0;
+        state->recount_mismatch = 0;
     }
 }
 
@@ -187,7 +197,8 @@ constexpr int kMaxRansacN = 16;
 __global__ void __launch_bounds__(128)
 ransac_fit_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m,
                   const int32_t* __restrict__ minimal, uint64_t seed, int h0, int w, int ransac_n,
-                  const RansacState* __restrict__ state, double* __restrict__ Tw) {
+                  const RansacState* __restrict__ state, double* __restrict__ Tw, double thr2,
+                  __nv_bfloat16* __restrict__ Apack, float* __restrict__ band) {
     if (state && h0 >= state->budget) return;
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= w) return;
@@ -199,6 +210,14 @@ ransac_fit_kernel(const float4* __restrict__ src4, const float4* __restrict__ tg
     double T12[12];
     umeyama_fit(src4, tgt4, idx, ransac_n, T12);
     for (int t = 0; t < 12; ++t) Tw[(size_t)j * 12 + t] = T12[t];
+    if (Apack) {
+        // weight row + rounding band of the tensor-core scoring (ransac_internal.cuh)
+        const double inv = 1.0 / (double)m;
+        const double cs[3] = {state->csum[0] * inv, state->csum[1] * inv, state->csum[2] * inv};
+        const double cq[3] = {state->csum[3] * inv, state->csum[4] * inv, state->csum[5] * inv};
+        ransac_tc_write_weights(T12, cs, cq, thr2, (double)__uint_as_float(state->smaxc_bits),
+                                (double)__uint_as_float(state->tmaxc_bits), j, Apack, band);
+    }
 }
 
 __global__ void ransac_draw_kernel(uint64_t seed, int m, size_t total, int32_t* __restrict__ out) {
@@ -242,13 +261,8 @@ __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
     return d;
 }
 
-// the oracle's float64 evaluation (unfused, same association order) of one pair
 __device__ __noinline__ double ransac_exact_d2(const double* __restrict__ Td, float4 s, float4 q) {
-    const double x = s.x, y = s.y, z = s.z;
-    double f0 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[0], x), __dmul_rn(Td[1], y)), __dmul_rn(Td[2], z)), Td[3]), (double)q.x);
-    double f1 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[4], x), __dmul_rn(Td[5], y)), __dmul_rn(Td[6], z)), Td[7]), (double)q.y);
-    double f2 = __dsub_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Td[8], x), __dmul_rn(Td[9], y)), __dmul_rn(Td[10], z)), Td[11]), (double)q.z);
-    return __dadd_rn(__dadd_rn(__dmul_rn(f0, f0), __dmul_rn(f1, f1)), __dmul_rn(f2, f2));
+    return ransac_exact_d2_inl(Td, s, q);
 }
 
 template <int NP>
@@ -397,7 +411,8 @@ constexpr int kFoldThreads = 1024;
 __global__ void __launch_bounds__(kFoldThreads)
 ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, const double* __restrict__ Tw,
                    int h0, int w, int m, int ransac_n, int adaptive, double conf, RansacState* __restrict__ state,
-                   int32_t* __restrict__ counts, double* __restrict__ sums, double* __restrict__ dev_work) {
+                   int32_t* __restrict__ counts, double* __restrict__ sums, double* __restrict__ dev_work,
+                   const float4* __restrict__ src4, const float4* __restrict__ tgt4, double thr2d) {
     if (h0 >= state->budget) return;
     __shared__ int s_scan[kFoldThreads];
     __shared__ int s_stop;
@@ -454,52 +469,83 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
     }
     __syncthreads();
     const int stop = s_stop;
-    // 4. best over [h0, stop)
-    int bc = -1, bh = 0x7fffffff;
-    double br = 0.0;
+    // 4. the best of [h0, stop): highest count; among hypotheses tied at that count the lowest
+    //    rmse, first wins exact ties.  The streamed sums are approximate (fp32 / tensor-core
+    //    values), so the sum of every hypothesis tied at the top count is recomputed here with the
+    //    oracle's float64 expression: the tie-break, best_sum and best_rmse are exact.
+    int cm = -1;
     for (int j = tid; j < w && h0 + j < stop; j += kFoldThreads) {
         const int c = pc[j];
-        const double sm = ps[j];
-        const double r = c > 0 ? sqrt(sm / (double)c) : 0.0;
         if (counts) counts[h0 + j] = c;
-        if (sums) sums[h0 + j] = sm;
-        if (ransac_better(c, r, h0 + j, bc, br, bh)) { bc = c; br = r; bh = h0 + j; }
+        if (sums) sums[h0 + j] = ps[j];
+        cm = max(cm, c);
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        int oc = __shfl_xor_sync(0xffffffffu, bc, o);
-        double orr = __shfl_xor_sync(0xffffffffu, br, o);
-        int oh = __shfl_xor_sync(0xffffffffu, bh, o);
-        if (ransac_better(oc, orr, oh, bc, br, bh)) { bc = oc; br = orr; bh = oh; }
-    }
-    if (lane == 0) { s_wc[warp] = bc; s_wr[warp] = br; s_wh[warp] = bh; }
+    for (int o = 16; o > 0; o >>= 1) cm = max(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+    if (lane == 0) s_wc[warp] = cm;
     __syncthreads();
-    if (warp == 0) {
-        bc = s_wc[lane]; br = s_wr[lane]; bh = s_wh[lane];
-        for (int o = 16; o > 0; o >>= 1) {
-            int oc = __shfl_xor_sync(0xffffffffu, bc, o);
-            double orr = __shfl_xor_sync(0xffffffffu, br, o);
-            int oh = __shfl_xor_sync(0xffffffffu, bh, o);
-            if (ransac_better(oc, orr, oh, bc, br, bh)) { bc = oc; br = orr; bh = oh; }
-        }
-        // the best of the earlier waves keeps exact ties (lower hypothesis index); the default
-        // result (count 0, rmse 0) is only replaced by a hypothesis with inliers
-        const bool improve = bc >= 0 && (bc > state->best_count || (bc == state->best_count && br < state->best_rmse));
-        if (improve && lane < 12) state->T[lane] = Tw[(size_t)(bh - h0) * 12 + lane];
-        __syncwarp();
-        if (lane == 0) {
-            int best_count = state->best_count;
-            if (improve) {
-                state->best_count = bc;
-                state->best_rmse = br;
-                state->best_sum = ps[bh - h0];
-                state->best_h = bh;
-                best_count = bc;
+    cm = s_wc[0];
+    for (int i = 1; i < 32; ++i) cm = max(cm, s_wc[i]);
+    __syncthreads();
+    const int prev_best = state->best_count;
+    int bj = -1;
+    double bsum = 0.0, brm = 0.0;
+    if (cm > 0 && cm >= prev_best) {
+        const int nrange = min(w, stop - h0);
+        int last = -1;
+        for (;;) {
+            int nxt = 0x7fffffff;
+            for (int j = tid; j < nrange; j += kFoldThreads)
+                if (j > last && pc[j] == cm) { nxt = j; break; }
+            for (int o = 16; o > 0; o >>= 1) nxt = min(nxt, __shfl_xor_sync(0xffffffffu, nxt, o));
+            if (lane == 0) s_wh[warp] = nxt;
+            __syncthreads();
+            nxt = s_wh[0];
+            for (int i = 1; i < 32; ++i) nxt = min(nxt, s_wh[i]);
+            __syncthreads();
+            if (nxt == 0x7fffffff) break;
+            last = nxt;
+            const double* Tj = Tw + (size_t)nxt * 12;
+            double sm = 0.0;
+            int cn = 0;
+            for (int i = tid; i < m; i += kFoldThreads) {
+                const double dd = ransac_exact_d2(Tj, src4[i], tgt4[i]);
+                if (dd < thr2d) { sm += dd; ++cn; }
             }
-            int budget = budget_in;
-            if (adaptive) budget = min(budget, ransac_budget_from_count(best_count, m, ransac_n, conf, budget_in));
-            state->budget = budget;
-            state->n_eval = stop;
+            for (int o = 16; o > 0; o >>= 1) {
+                sm += __shfl_xor_sync(0xffffffffu, sm, o);
+                cn += __shfl_xor_sync(0xffffffffu, cn, o);
+            }
+            if (lane == 0) { s_wr[warp] = sm; s_wc[warp] = cn; }
+            __syncthreads();
+            sm = 0.0;
+            cn = 0;
+            for (int i = 0; i < 32; ++i) { sm += s_wr[i]; cn += s_wc[i]; }
+            __syncthreads();
+            const double r = sqrt(sm / (double)cm);
+            if (tid == 0) {
+                if (cn != cm) atomicAdd(&state->recount_mismatch, 1);
+                ps[nxt] = sm;
+                if (sums) sums[h0 + nxt] = sm;
+            }
+            if (bj < 0 || r < brm) { bj = nxt; bsum = sm; brm = r; }
         }
+    }
+    if (tid == 0) {
+        // the best of the earlier waves keeps exact ties (lower hypothesis index)
+        const bool improve = bj >= 0 && (cm > prev_best || (cm == prev_best && brm < state->best_rmse));
+        int best_count = prev_best;
+        if (improve) {
+            for (int t = 0; t < 12; ++t) state->T[t] = Tw[(size_t)bj * 12 + t];
+            state->best_count = cm;
+            state->best_rmse = brm;
+            state->best_sum = bsum;
+            state->best_h = h0 + bj;
+            best_count = cm;
+        }
+        int budget = budget_in;
+        if (adaptive) budget = min(budget, ransac_budget_from_count(best_count, m, ransac_n, conf, budget_in));
+        state->budget = budget;
+        state->n_eval = stop;
     }
 }
 
@@ -543,9 +589,13 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
     (void)n_tgt;
     const int wmax = 32768;
     const size_t pw_max = size_t(1) << 20;  // entries of the [P, w] partial count / sum arrays
-    constexpr int NP = 2;                   // hypothesis pairs per scoring thread
+    constexpr int NP = 2;                   // hypothesis pairs per SIMT scoring thread
+    const bool use_tc = ctx->ransac_variant != 1 && m < (1 << 24);
+    const int m_pad = cb_div_up(max(m, 1), kRtTileN) * kRtTileN;
     size_t need = cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) +
                   cb_align((size_t)wmax * 12 * 8) + cb_align(pw_max * 4) + cb_align(pw_max * 8);
+    if (use_tc)
+        need += cb_align((size_t)m_pad * kRtKP * 2) + cb_align((size_t)(wmax + 256) * kRtKP * 2) + cb_align((size_t)wmax * 4);
     if ((rc = cb_reserve(ctx, need))) return rc;
     RansacState* state = cb_alloc_t<RansacState>(ctx, 1);
     if (!state) return CB_ENOMEM;
@@ -561,38 +611,70 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         int32_t* pc = cb_alloc_t<int32_t>(ctx, pw_max);
         double* ps = cb_alloc_t<double>(ctx, pw_max);
         if (!src4 || !tgt4 || !Tw || !pc || !ps) return CB_ENOMEM;
+        __nv_bfloat16 *Apack = nullptr, *Bpack = nullptr;
+        float* band = nullptr;
+        if (use_tc) {
+            Bpack = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)m_pad * kRtKP);
+            Apack = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)(wmax + 256) * kRtKP);
+            band = cb_alloc_t<float>(ctx, wmax);
+            if (!Apack || !Bpack || !band) return CB_ENOMEM;
+        }
         ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, src_idx, tgt_idx, m, src4, tgt4,
                                                               state);
         CB_LAUNCH_CHECK(ctx);
+        if (use_tc && (rc = ransac_tc_pack_corr_launch(ctx, src4, tgt4, m, state, Bpack, st))) return rc;
         const double thr2 = max_dist * max_dist;
         int h0 = 0;
         for (int wave = 0; h0 < h_total; ++wave) {
             const int w = min(ransac_wave_size(wave), h_total - h0);
-            const int groups = cb_div_up(w, 128 * 2 * NP);
-            int P = cb_div_up(8 * ctx->sm_count, groups);  // ~2 waves at 4 resident blocks per SM
-            P = max(1, min(min(P, (int)(pw_max / (size_t)w)), cb_div_up(m, kScoreTile)));
-            int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
-            P = cb_div_up(m, split);
             {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_FIT, 0.0, st);
                 ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
-                                                                     state, Tw);
+                                                                     state, Tw, thr2, Apack, band);
                 CB_LAUNCH_CHECK(ctx);
             }
-            {
+            int P = 1;
+            if (use_tc) {
+                cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
+                if ((rc = ransac_tc_score_launch(ctx, Apack, Bpack, band, Tw, src4, tgt4, m, h0, w, thr2, state, pc, ps,
+                                                 &P, st)))
+                    return rc;
+            } else {
+                const int groups = cb_div_up(w, 128 * 2 * NP);
+                P = cb_div_up(8 * ctx->sm_count, groups);  // ~2 waves at 4 resident blocks per SM
+                P = max(1, min(min(P, (int)(pw_max / (size_t)w)), cb_div_up(m, kScoreTile)));
+                int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
+                P = cb_div_up(m, split);
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
                 ransac_score_kernel<NP><<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state,
                                                                      pc, ps);
                 CB_LAUNCH_CHECK(ctx);
             }
             ransac_fold_kernel<<<1, kFoldThreads, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
-                                                 counts, sums, ctx->dev_work);
+                                                 counts, sums, ctx->dev_work, src4, tgt4, thr2);
             CB_LAUNCH_CHECK(ctx);
             h0 += w;
         }
     }
     ransac_finish_kernel<<<1, 32, 0, st>>>(state, T, stats);
     CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+extern "C" int cb_set_ransac_variant(cb_ctx* ctx, int variant) {
+    if (!ctx || variant < 0 || variant > 2) return CB_EINVAL;
+    ctx->ransac_variant = variant;
+    return CB_OK;
+}
+
+extern "C" const char* cb_ransac_variant(const cb_ctx* ctx) {
+    return (ctx && ctx->ransac_variant == 1) ? "simt" : "tcgen05";
+}
+
+extern "C" int cb_ransac_debug_dump(cb_ctx* ctx, float* u_out, int ld) {
+    if (!ctx || (u_out && ld <= 0)) return CB_EINVAL;
+    ctx->ransac_dump = u_out;
+    ctx->ransac_dump_ld = ld;
     return CB_OK;
 }
 
@@ -627,7 +709,7 @@ extern "C" int cb_fit_minimal(cb_ctx* ctx, const float* src_xyz, const float* tg
     ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, nullptr, nullptr, m, src4, tgt4, state);
     CB_LAUNCH_CHECK(ctx);
     ransac_fit_kernel<<<cb_div_up(h_total, 128), 128, 0, st>>>(src4, tgt4, m, minimal, 0, 0, h_total, ransac_n,
-                                                               nullptr, Tw);
+                                                               nullptr, Tw, 0.0, nullptr, nullptr);
     CB_LAUNCH_CHECK(ctx);
     ransac_expand_T_kernel<<<cb_div_up(h_total * 16, 256), 256, 0, st>>>(Tw, h_total, T_all);
     CB_LAUNCH_CHECK(ctx);

@@ -1,0 +1,402 @@
+// K3 scoring on the 5th-generation tensor cores.
+//
+// The inlier test of hypothesis h on correspondence c, u = |R_h s_c + t_h - q_c|^2 - thr^2 < 0, is
+// one inner product between a per-hypothesis weight row and a per-correspondence feature row
+// (ransac_internal.cuh), so a whole wave is the GEMM  U[h, c] = A[h, :] . B[c, :]  in split bf16
+// (three bf16 pieces per factor, six products per bilinear term: fp32-grade accuracy), fp32 accumulate.
+// The epilogue never stores U: each thread owns one hypothesis (one TMEM lane) and folds its row
+// into an inlier count and a sum as it streams out of tensor memory.
+//
+// Exactness: |U - u_float64| <= band[h] (a rigorous per-hypothesis rounding bound).  Evaluations
+// with |U| <= band are queued in shared memory and re-decided by the oracle's unfused float64
+// expression on the raw float32 points, so the COUNT is exactly the float64 count; everything
+// outside the band (> 99.9 %) is decided by the tensor-core value alone.
+//
+// CTA = 256 hypotheses (two A tiles) x one split of the correspondences, 320 threads:
+//   warp 8  producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
+//   warp 9  one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
+//           a double-buffered TMEM accumulator (2 stages x 2 A tiles x 128 columns = 512)
+//   warps 0-7 epilogue: warp w reads lane quadrant w%4 of A tile w/4, 32 columns per tcgen05.ld
+#include "ransac_internal.cuh"
+
+#include <math.h>
+
+namespace {
+
+constexpr int kHT = 2;            // A tiles (of 128 hypotheses) per CTA
+constexpr int kStages = 3;        // shared-memory ring of B tiles
+constexpr int kThreads = 320;
+constexpr int kListCap = 4096;    // queued in-band evaluations per CTA (overflow is settled inline)
+constexpr int kListDrain = 2048;  // drain the queue at the next tile boundary once it holds this many
+constexpr uint32_t kATileBytes = kRtTileM * kRtKP * 2;  // 24 KB
+constexpr uint32_t kBTileBytes = kRtTileN * kRtKP * 2;  // 24 KB
+
+// ------------------------------------------------------------------------------ B pack
+// One thread per (correspondence row, 8-column group).  Rows >= m are padding: n = +big so the
+// evaluation is never an inlier and never inside a band.
+__global__ void __launch_bounds__(256)
+ransac_tc_pack_corr_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int m_pad,
+                           RansacState* __restrict__ state, __nv_bfloat16* __restrict__ Bpack) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    constexpr int kGroups = kRtKP / 8;
+    const int row = (int)(gid / kGroups), kc = (int)(gid % kGroups);
+    float ns = 0.f, nq = 0.f;
+    if (row < m_pad) {
+        __nv_bfloat16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __float2bfloat16_rn(0.f);
+        if (row < m) {
+            const double inv = 1.0 / (double)m;
+            const float4 s4 = src4[row], q4 = tgt4[row];
+            const double s[3] = {(double)s4.x - state->csum[0] * inv, (double)s4.y - state->csum[1] * inv,
+                                 (double)s4.z - state->csum[2] * inv};
+            const double q[3] = {(double)q4.x - state->csum[3] * inv, (double)q4.y - state->csum[4] * inv,
+                                 (double)q4.z - state->csum[5] * inv};
+            const double n = s[0] * s[0] + s[1] * s[1] + s[2] * s[2] + q[0] * q[0] + q[1] * q[1] + q[2] * q[2];
+            if (kc == 0) {
+                // maxima of the centred norms, rounded up, for the fit kernel's band
+                ns = (float)sqrt(s[0] * s[0] + s[1] * s[1] + s[2] * s[2]) * 1.000001f;
+                nq = (float)sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]) * 1.000001f;
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int col = kc * 8 + e;
+                if (col < 90) {
+                    const int k = col % kRtTerms, part = col / kRtTerms;  // part: pa pb pa pc pa pb
+                    const double phi = k < 9 ? q[k / 3] * s[k % 3] : (k < 12 ? s[k - 9] : q[k - 12]);
+                    __nv_bfloat16 pa, pb, pc;
+                    rt_split3(phi, pa, pb, pc);
+                    v[e] = (part == 1 || part == 5) ? pb : (part == 3 ? pc : pa);
+                } else if (col < 93) {
+                    __nv_bfloat16 a, b, c;
+                    rt_split3(n, a, b, c);
+                    v[e] = col == 90 ? a : (col == 91 ? b : c);
+                } else {
+                    v[e] = __float2bfloat16_rn(1.f);
+                }
+            }
+        } else if (kc == 11) {
+            v[2] = __float2bfloat16_rn(1e30f);  // column 90
+        }
+        const int tile = row / kRtTileN, r = row % kRtTileN;
+        char* dst = reinterpret_cast<char*>(Bpack) + (size_t)tile * kBTileBytes + tc::tile_offset(kRtTileN, r, kc);
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ns = fmaxf(ns, __shfl_xor_sync(0xffffffffu, ns, o));
+        nq = fmaxf(nq, __shfl_xor_sync(0xffffffffu, nq, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (ns > 0.f) atomicMax(&state->smaxc_bits, __float_as_uint(ns));
+        if (nq > 0.f) atomicMax(&state->tmaxc_bits, __float_as_uint(nq));
+    }
+}
+
+// ------------------------------------------------------------------------------ scoring
+struct RtCtl {
+    uint64_t a_full, full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+    uint32_t tmem_base;
+    int list_n;
+};
+
+// queue entry (int2): x = CTA-local hypothesis row (8 bits) << 24 | correspondence index (24 bits),
+// y = the tensor-core value of u (float bits)
+
+__device__ __forceinline__ float fma_sat(float a, float b, float c) {
+    float d;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+constexpr float kNegBig = -1.2676506e30f;  // -2^100: fma.sat(u, kNegBig, 0) = 1 for u < 0, else 0
+
+// what the streaming pass added for a value u: (g, g*u)
+__device__ __forceinline__ float rt_gate(float u) { return fma_sat(u, kNegBig, 0.f); }
+
+// exact decision for one evaluation; returns the correction (exact - streamed) of count and sum
+__device__ __forceinline__ void rt_exact_delta(const double* __restrict__ Tj, const float4* __restrict__ src4,
+                                               const float4* __restrict__ tgt4, int col, float u, double thr2d,
+                                               double& dc, double& ds) {
+    const double dd = ransac_exact_d2_inl(Tj, src4[col], tgt4[col]);
+    const bool in = dd < thr2d;
+    const float g = rt_gate(u);
+    dc = (in ? 1.0 : 0.0) - (double)g;
+    ds = (in ? dd - thr2d : 0.0) - (double)g * (double)u;
+}
+
+// the CTA's queue is full: settle one in-band evaluation on the spot
+__device__ __noinline__ void rt_overflow(int col, float u, const double* __restrict__ Tj, const float4* __restrict__ src4,
+                                         const float4* __restrict__ tgt4, double thr2d, double& dcnt, double& dsum) {
+    double dc, ds;
+    rt_exact_delta(Tj, src4, tgt4, col, u, thr2d, dc, ds);
+    dcnt += dc;
+    dsum += ds;
+}
+
+// all 256 epilogue threads: re-decide the queued evaluations exactly, corrections into s_dcnt/s_dsum
+__device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s_dcnt, double* s_dsum, int jcta, int w,
+                                         const double* __restrict__ Tw, const float4* __restrict__ src4,
+                                         const float4* __restrict__ tgt4, double thr2d) {
+    const int nlist = min(*(volatile int*)&ctl->list_n, kListCap);
+    for (int i = threadIdx.x; i < nlist; i += 256) {
+        const int2 en = list[i];
+        const int row = (en.x >> 24) & 0xff, col = en.x & 0xffffff;
+        double dc, ds;
+        rt_exact_delta(Tw + (size_t)min(jcta + row, w - 1) * 12, src4, tgt4, col, __int_as_float(en.y), thr2d, dc, ds);
+        atomicAdd(&s_dcnt[row], dc);
+        atomicAdd(&s_dsum[row], ds);
+    }
+}
+
+template <bool DUMP>
+__global__ void __launch_bounds__(kThreads, 1)
+ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
+                       const float* __restrict__ band_g, const double* __restrict__ Tw,
+                       const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int ntiles_total,
+                       int tiles_per_split, int h0, int w, double thr2d, const RansacState* __restrict__ state,
+                       int32_t* __restrict__ pc, double* __restrict__ ps, float* __restrict__ dump, int dump_ld) {
+    if (h0 >= state->budget) return;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    unsigned char* sA = smem;                               // kHT A tiles
+    unsigned char* sB = smem + kHT * kATileBytes;           // kStages B tiles
+    int2* list = reinterpret_cast<int2*>(sB + kStages * kBTileBytes);
+    double* s_dsum = reinterpret_cast<double*>(list + kListCap);
+    double* s_dcnt = s_dsum + kHT * kRtTileM;
+    RtCtl* ctl = reinterpret_cast<RtCtl*>(s_dcnt + kHT * kRtTileM);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t0 = blockIdx.y * tiles_per_split;
+    const int t1 = min(ntiles_total, t0 + tiles_per_split);
+    const int ntiles = t1 - t0;
+    const int jcta = blockIdx.x * (kHT * kRtTileM);  // first hypothesis (wave-relative) of this CTA
+
+    if (threadIdx.x == 0) {
+        tc::mbar_init(&ctl->a_full, 1);
+        for (int i = 0; i < kStages; ++i) {
+            tc::mbar_init(&ctl->full[i], 1);
+            tc::mbar_init(&ctl->empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(&ctl->tmem_full[i], 1);
+            tc::mbar_init(&ctl->tmem_empty[i], 8);
+        }
+        ctl->list_n = 0;
+        tc::fence_barrier_init();
+    }
+    if (threadIdx.x < kHT * kRtTileM) { s_dsum[threadIdx.x] = 0.0; s_dcnt[threadIdx.x] = 0.0; }
+    if (warp == 8) tc::tmem_alloc(&ctl->tmem_base, 512);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tbase = ctl->tmem_base;
+
+    if (warp == 8) {
+        // ===== producer =====
+        if (lane == 0) {
+            tc::mbar_arrive_expect_tx(&ctl->a_full, kHT * kATileBytes);
+            tc::bulk_g2s(sA, reinterpret_cast<const char*>(Apack) + (size_t)blockIdx.x * kHT * kATileBytes,
+                         kHT * kATileBytes, &ctl->a_full);
+            for (int it = 0; it < ntiles; ++it) {
+                const int st = it % kStages, use = it / kStages;
+                tc::mbar_wait(&ctl->empty[st], (use & 1) ^ 1);
+                tc::mbar_arrive_expect_tx(&ctl->full[st], kBTileBytes);
+                tc::bulk_g2s(sB + st * kBTileBytes, reinterpret_cast<const char*>(Bpack) + (size_t)(t0 + it) * kBTileBytes,
+                             kBTileBytes, &ctl->full[st]);
+            }
+        }
+    } else if (warp == 9) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::idesc_bf16(kRtTileM, kRtTileN);
+            constexpr uint32_t LBO = (kRtTileM / 8) * 128;  // both operands: 128-row tiles
+            const uint32_t a_addr = tc::smem_u32(sA);
+            tc::mbar_wait(&ctl->a_full, 0);
+            for (int it = 0; it < ntiles; ++it) {
+                const int st = it % kStages, use = it / kStages;
+                const int ts = it & 1, tuse = it >> 1;
+                tc::mbar_wait(&ctl->full[st], use & 1);
+                tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t b_addr = tc::smem_u32(sB + st * kBTileBytes);
+#pragma unroll
+                for (int a = 0; a < kHT; ++a) {
+#pragma unroll
+                    for (int ks = 0; ks < kRtKP / 16; ++ks) {
+                        const uint64_t ad = tc::smem_desc(a_addr + a * kATileBytes + ks * 2 * LBO, LBO, 128);
+                        const uint64_t bd = tc::smem_desc(b_addr + ks * 2 * LBO, LBO, 128);
+                        tc::mma_bf16(tbase + (ts * kHT + a) * kRtTileN, ad, bd, idesc, ks > 0);
+                    }
+                }
+                tc::mma_commit(&ctl->empty[st]);
+                tc::mma_commit(&ctl->tmem_full[ts]);
+            }
+        }
+    } else {
+        // ===== epilogue: 256 threads, one hypothesis each =====
+        const int a = warp >> 2;                           // A tile of this warp
+        const int rloc = a * kRtTileM + (warp & 3) * 32 + lane;  // row inside the CTA
+        const int j = jcta + rloc;                         // wave-relative hypothesis
+        const bool valid = j < w;
+        const float band = valid ? band_g[j] : -1.f;
+        const double* Tj = Tw + (size_t)min(j, w - 1) * 12;
+        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN;
+        double cnt_d = 0.0, sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
+        for (int it = 0; it < ntiles; ++it) {
+            const int ts = it & 1, tuse = it >> 1;
+            tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
+            tc::fence_after_sync();
+            const int col0 = (t0 + it) * kRtTileN;
+            f32x2 c2 = pk2(0.f, 0.f), s2 = pk2(0.f, 0.f);
+#pragma unroll 1
+            for (int cb = 0; cb < kRtTileN / 32; ++cb) {
+                float v[32];
+                tc::tmem_ld32(lane_addr + ts * (kHT * kRtTileN) + cb * 32, v);
+                tc::tmem_ld_wait();
+                float bm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+#pragma unroll
+                for (int e = 0; e < 32; e += 2) {
+                    const float g0 = rt_gate(v[e]), g1 = rt_gate(v[e + 1]);
+                    const f32x2 g = pk2(g0, g1);
+                    c2 = add2(c2, g);
+                    s2 = fma2(g, pk2(v[e], v[e + 1]), s2);
+                    bm[e >> 3] = fminf(bm[e >> 3], fminf(fabsf(v[e]), fabsf(v[e + 1])));
+                }
+                if (DUMP) {
+                    if (valid)
+                        for (int e = 0; e < 32; ++e)
+                            if (col0 + cb * 32 + e < m) dump[(size_t)j * dump_ld + col0 + cb * 32 + e] = v[e];
+                }
+                if (fminf(fminf(bm[0], bm[1]), fminf(bm[2], bm[3])) <= band) {
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        if (bm[g8] <= band) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const float u = v[g8 * 8 + e];
+                                if (fabsf(u) <= band) {
+                                    const int col = col0 + cb * 32 + g8 * 8 + e;
+                                    const int pos = atomicAdd(&ctl->list_n, 1);
+                                    if (pos < kListCap) list[pos] = make_int2((rloc << 24) | col, __float_as_int(u));
+                                    else rt_overflow(col, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            // accumulator stage drained: hand it back to the MMA warp
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
+            float x, y;
+            unpk2(c2, x, y);
+            cnt_d += (double)x + (double)y;
+            unpk2(s2, x, y);
+            sum_d += (double)x + (double)y;
+            // every 16 tiles: if the queue is half full (a CTA-uniform decision) drain it
+            if ((it & 15) != 15) continue;
+            named_bar_sync(1, 256);
+            if (*(volatile int*)&ctl->list_n >= kListDrain) {
+                rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
+                named_bar_sync(1, 256);
+                if (threadIdx.x == 0) ctl->list_n = 0;
+                named_bar_sync(1, 256);
+            }
+        }
+        // settle the queued in-band evaluations of the whole CTA
+        named_bar_sync(1, 256);
+        rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
+        named_bar_sync(1, 256);
+        if (valid) {
+            const double c = cnt_d + dcnt + s_dcnt[rloc];
+            const long long ci = llrint(c);
+            pc[(size_t)blockIdx.y * w + j] = (int)ci;
+            // sum of squared inlier distances = sum (d^2 - thr^2) + count * thr^2
+            ps[(size_t)blockIdx.y * w + j] = sum_d + dsum + s_dsum[rloc] + (double)ci * thr2d;
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 8) tc::tmem_dealloc(tbase, 512);
+}
+
+constexpr size_t kScoreSmem = kHT * kATileBytes + kStages * kBTileBytes + kListCap * sizeof(int2) +
+                              2 * kHT * kRtTileM * sizeof(double) + sizeof(RtCtl) + 64;
+
+void rt_split_plan(const cb_ctx* ctx, int m, int w, int* P, int* tiles_per_split) {
+    const int ntiles = cb_div_up(m, kRtTileN);
+    const int groups = cb_div_up(w, kHT * kRtTileM);
+    int p = max(1, ctx->sm_count / groups);  // one CTA per SM (TMEM: 512 columns each)
+    p = min(p, ntiles);
+    const int tps = cb_div_up(ntiles, p);
+    *tiles_per_split = tps;
+    *P = cb_div_up(ntiles, tps);
+}
+
+}  // namespace
+
+int ransac_tc_max_splits(const cb_ctx* ctx, int m, int w) {
+    int P, tps;
+    rt_split_plan(ctx, m, w, &P, &tps);
+    return P;
+}
+
+int ransac_tc_pack_corr_launch(cb_ctx* ctx, const float4* src4, const float4* tgt4, int m, RansacState* state,
+                               __nv_bfloat16* Bpack, cudaStream_t st) {
+    const int m_pad = cb_div_up(m, kRtTileN) * kRtTileN;
+    const size_t threads = (size_t)m_pad * (kRtKP / 8);
+    ransac_tc_pack_corr_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(src4, tgt4, m, m_pad, state, Bpack);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
+int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_bfloat16* Bpack, const float* band,
+                           const double* Tw, const float4* src4, const float4* tgt4, int m, int h0, int w,
+                           double thr2, const RansacState* state, int32_t* pc, double* ps, int* P_out,
+                           cudaStream_t st) {
+    if (m >= (1 << 24)) CB_FAIL(ctx, CB_EUNSUPPORTED, "tensor-core RANSAC scoring holds at most 2^24 correspondences");
+    int P, tps;
+    rt_split_plan(ctx, m, w, &P, &tps);
+    *P_out = P;
+    float* dump = ctx->ransac_dump;
+    const int dump_ld = ctx->ransac_dump_ld;
+    cudaError_t e;
+    if (dump) {
+        e = cudaFuncSetAttribute(ransac_tc_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
+        if (e == cudaSuccess)
+            ransac_tc_score_kernel<true><<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
+                Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps,
+                dump + (size_t)h0 * dump_ld, dump_ld);
+    } else {
+        e = cudaFuncSetAttribute(ransac_tc_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kScoreSmem);
+        if (e == cudaSuccess)
+            ransac_tc_score_kernel<false><<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
+                Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps, nullptr, 0);
+    }
+    if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "ransac_tc_score_kernel: %s", cudaGetErrorString(e));
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}

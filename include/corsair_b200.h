@@ -58,6 +58,14 @@ int64_t cb_launch_count(const cb_ctx* ctx);
 const char* cb_knn_variant(const cb_ctx* ctx);
 /* force a kNN candidate variant (0 = auto, 1 = simt fp32, 2 = tcgen05 bf16x3); for tests/bench */
 int cb_set_knn_variant(cb_ctx* ctx, int variant);
+/* RANSAC scoring variant: "tcgen05" (split-bf16 GEMM, default) or "simt" (packed fp32);
+ * cb_set_ransac_variant: 0 = auto, 1 = simt, 2 = tcgen05; for tests/bench */
+const char* cb_ransac_variant(const cb_ctx* ctx);
+int cb_set_ransac_variant(cb_ctx* ctx, int variant);
+/* test hook: the next cb_ransac calls of this ctx (tcgen05 variant) also store the raw
+ * tensor-core values U[h, c] = d^2 - max_dist^2 (before the exact in-band re-decision) into the
+ * device array u_out [h_total, ld] (ld >= m); NULL switches the dump off */
+int cb_ransac_debug_dump(cb_ctx* ctx, float* u_out, int ld);
 /* diagnostic: rows of the most recent E1 kNN problem of this ctx that failed the re-rank's proof
  * obligation and were recomputed by the exact brute-force kernel (synchronises the stream);
  * -1 if no E1 problem has run since the last arena growth */
