@@ -198,11 +198,19 @@ __global__ void __launch_bounds__(128)
 ransac_fit_kernel(const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m,
                   const int32_t* __restrict__ minimal, uint64_t seed, int h0, int w, int ransac_n,
                   const RansacState* __restrict__ state, double* __restrict__ Tw, double thr2,
-                  __nv_bfloat16* __restrict__ Apack, float* __restrict__ band) {
+                  __nv_bfloat16* __restrict__ Apack, float* __restrict__ band, int32_t* __restrict__ tot_c,
+                  double* __restrict__ tot_s) {
     if (state && h0 >= state->budget) return;
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= w) return;
     const int h = h0 + j;
+    if (tot_c) {
+        // totals the tensor-core scoring adds into; hypotheses at or beyond the budget are not
+        // fitted or scored (the fold never looks at them)
+        tot_c[j] = 0;
+        tot_s[j] = 0.0;
+        if (h >= state->budget) return;
+    }
     int idx[kMaxRansacN];
     for (int t = 0; t < ransac_n; ++t)
         idx[t] = minimal ? minimal[(size_t)h * ransac_n + t]
@@ -401,7 +409,7 @@ __device__ __forceinline__ bool ransac_better(int c, double r, int h, int bc, do
 // One block of 1024 threads folds hypotheses h0..h0+w-1 with the semantics of the sequential
 // scan: process h in order while h < budget; an improvement (count up, or equal count and lower
 // rmse) may shrink the budget, which depends only on the best count so far.  Parallel form:
-//   1. totals per hypothesis (sum of the P partials), written in place into row 0 of pc/ps
+//   1. totals per hypothesis (sum of the P partials) staged in shared memory
 //   2. block max-scan of per-segment maximum counts -> the best count BEFORE each segment
 //   3. every thread walks its contiguous segment with the running best count and finds the
 //      first h with h >= budget(best count so far); block-min -> where the scan stops
@@ -418,6 +426,7 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
     __shared__ int s_stop;
     __shared__ int s_wc[32], s_wh[32];
     __shared__ double s_wr[32];
+    extern __shared__ int s_cnt[];  // [w] total inlier counts of the wave (every later pass reads these)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int budget_in = state->budget;
     const int prev_count = state->best_count;
@@ -433,15 +442,15 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
             cnt += pc[(size_t)p * w + j];
             sm += ps[(size_t)p * w + j];
         }
-        pc[j] = cnt;
-        ps[j] = sm;
+        s_cnt[j] = cnt;
+        if (P > 1) ps[j] = sm;
     }
     __syncthreads();
     // 2. best count before each segment
     const int L = (w + kFoldThreads - 1) / kFoldThreads;
     const int j0 = min(w, tid * L), j1 = min(w, j0 + L);
     int seg_max = 0;
-    for (int j = j0; j < j1; ++j) seg_max = max(seg_max, pc[j]);
+    for (int j = j0; j < j1; ++j) seg_max = max(seg_max, s_cnt[j]);
     s_scan[tid] = seg_max;
     __syncthreads();
     for (int off = 1; off < kFoldThreads; off <<= 1) {
@@ -458,7 +467,7 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
         for (int j = j0; j < j1; ++j) {
             const int h = h0 + j;
             if (h >= b) { stop = h; break; }
-            const int c = pc[j];
+            const int c = s_cnt[j];
             if (c > run) {
                 run = c;
                 if (adaptive) b = min(b, ransac_budget_from_count(run, m, ransac_n, conf, budget_in));
@@ -475,7 +484,7 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
     //    oracle's float64 expression: the tie-break, best_sum and best_rmse are exact.
     int cm = -1;
     for (int j = tid; j < w && h0 + j < stop; j += kFoldThreads) {
-        const int c = pc[j];
+        const int c = s_cnt[j];
         if (counts) counts[h0 + j] = c;
         if (sums) sums[h0 + j] = ps[j];
         cm = max(cm, c);
@@ -495,7 +504,7 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
         for (;;) {
             int nxt = 0x7fffffff;
             for (int j = tid; j < nrange; j += kFoldThreads)
-                if (j > last && pc[j] == cm) { nxt = j; break; }
+                if (j > last && s_cnt[j] == cm) { nxt = j; break; }
             for (int o = 16; o > 0; o >>= 1) nxt = min(nxt, __shfl_xor_sync(0xffffffffu, nxt, o));
             if (lane == 0) s_wh[warp] = nxt;
             __syncthreads();
@@ -569,10 +578,12 @@ __global__ void ransac_expand_T_kernel(const double* __restrict__ Tw, int h, dou
     T_all[i] = e < 12 ? Tw[(size_t)hh * 12 + e] : (e == 15 ? 1.0 : 0.0);
 }
 
-static int ransac_wave_size(int wave_index) {
-    int w = 4096;
-    for (int i = 1; i < wave_index && w < 32768; ++i) w <<= 1;  // 4096, 4096, 8192, 16384, 32768, ...
-    return w;
+// Waves of hypotheses: a small first wave (most adaptive runs stop inside it), then waves that give
+// every SM one 256-hypothesis CTA of the tensor-core scoring kernel.
+constexpr int kWaveFirst = 4096;
+static int ransac_wave_max(const cb_ctx* ctx) { return max(kWaveFirst, min(ctx->sm_count, 160) * 256); }
+static int ransac_wave_size(const cb_ctx* ctx, int wave_index) {
+    return wave_index == 0 ? kWaveFirst : ransac_wave_max(ctx);
 }
 
 extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const float* tgt_xyz, int n_tgt,
@@ -587,8 +598,8 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         CB_FAIL(ctx, CB_EINVAL, "cb_ransac: bad arguments (m=%d h=%d n=%d)", m, h_total, ransac_n);
     (void)n_src;
     (void)n_tgt;
-    const int wmax = 32768;
-    const size_t pw_max = size_t(1) << 20;  // entries of the [P, w] partial count / sum arrays
+    const int wmax = ransac_wave_max(ctx);
+    const size_t pw_max = size_t(5) << 18;  // entries of the [P, w] partial count / sum arrays
     constexpr int NP = 2;                   // hypothesis pairs per SIMT scoring thread
     const bool use_tc = ctx->ransac_variant != 1 && m < (1 << 24);
     const int m_pad = cb_div_up(max(m, 1), kRtTileN) * kRtTileN;
@@ -624,20 +635,22 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         CB_LAUNCH_CHECK(ctx);
         if (use_tc && (rc = ransac_tc_pack_corr_launch(ctx, src4, tgt4, m, state, Bpack, st))) return rc;
         const double thr2 = max_dist * max_dist;
+        CB_CUDA(ctx, cudaFuncSetAttribute(ransac_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(wmax * sizeof(int))));
         int h0 = 0;
         for (int wave = 0; h0 < h_total; ++wave) {
-            const int w = min(ransac_wave_size(wave), h_total - h0);
+            const int w = min(ransac_wave_size(ctx, wave), h_total - h0);
             {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_FIT, 0.0, st);
                 ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
-                                                                     state, Tw, thr2, Apack, band);
+                                                                     state, Tw, thr2, Apack, band,
+                                                                     use_tc ? pc : nullptr, use_tc ? ps : nullptr);
                 CB_LAUNCH_CHECK(ctx);
             }
             int P = 1;
             if (use_tc) {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
-                if ((rc = ransac_tc_score_launch(ctx, Apack, Bpack, band, Tw, src4, tgt4, m, h0, w, thr2, state, pc, ps,
-                                                 &P, st)))
+                if ((rc = ransac_tc_score_launch(ctx, Apack, Bpack, band, Tw, src4, tgt4, m, h0, w, thr2, state, pc, ps, st)))
                     return rc;
             } else {
                 const int groups = cb_div_up(w, 128 * 2 * NP);
@@ -650,7 +663,7 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
                                                                      pc, ps);
                 CB_LAUNCH_CHECK(ctx);
             }
-            ransac_fold_kernel<<<1, kFoldThreads, 0, st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
+            ransac_fold_kernel<<<1, kFoldThreads, (size_t)w * sizeof(int), st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
                                                  counts, sums, ctx->dev_work, src4, tgt4, thr2);
             CB_LAUNCH_CHECK(ctx);
             h0 += w;
@@ -709,7 +722,7 @@ extern "C" int cb_fit_minimal(cb_ctx* ctx, const float* src_xyz, const float* tg
     ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, nullptr, nullptr, m, src4, tgt4, state);
     CB_LAUNCH_CHECK(ctx);
     ransac_fit_kernel<<<cb_div_up(h_total, 128), 128, 0, st>>>(src4, tgt4, m, minimal, 0, 0, h_total, ransac_n,
-                                                               nullptr, Tw, 0.0, nullptr, nullptr);
+                                                               nullptr, Tw, 0.0, nullptr, nullptr, nullptr, nullptr);
     CB_LAUNCH_CHECK(ctx);
     ransac_expand_T_kernel<<<cb_div_up(h_total * 16, 256), 256, 0, st>>>(Tw, h_total, T_all);
     CB_LAUNCH_CHECK(ctx);

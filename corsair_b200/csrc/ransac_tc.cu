@@ -178,7 +178,8 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                        const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int ntiles_total,
                        int tiles_per_split, int h0, int w, double thr2d, const RansacState* __restrict__ state,
                        int32_t* __restrict__ pc, double* __restrict__ ps, float* __restrict__ dump, int dump_ld) {
-    if (h0 >= state->budget) return;
+    // hypotheses at or beyond the (device-side, shrinking) budget are never looked at by the fold
+    if (h0 + (int)blockIdx.x * (kHT * kRtTileM) >= state->budget) return;
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* sA = smem;                               // kHT A tiles
     unsigned char* sB = smem + kHT * kATileBytes;           // kStages B tiles
@@ -332,9 +333,10 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         if (valid) {
             const double c = cnt_d + dcnt + s_dcnt[rloc];
             const long long ci = llrint(c);
-            pc[(size_t)blockIdx.y * w + j] = (int)ci;
+            // totals over the correspondence splits (zeroed by the fit kernel)
+            atomicAdd(&pc[j], (int)ci);
             // sum of squared inlier distances = sum (d^2 - thr^2) + count * thr^2
-            ps[(size_t)blockIdx.y * w + j] = sum_d + dsum + s_dsum[rloc] + (double)ci * thr2d;
+            atomicAdd(&ps[j], sum_d + dsum + s_dsum[rloc] + (double)ci * thr2d);
         }
     }
     tc::fence_before_sync();
@@ -345,23 +347,27 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
 constexpr size_t kScoreSmem = kHT * kATileBytes + kStages * kBTileBytes + kListCap * sizeof(int2) +
                               2 * kHT * kRtTileM * sizeof(double) + sizeof(RtCtl) + 64;
 
+// Splits of the correspondence axis: one CTA per SM is resident (TMEM: 512 columns each), so the
+// kernel runs ceil(groups * P / SMs) rounds of CTAs that each stream ~1/P of the tiles; pick the P
+// with the shortest makespan (a small per-CTA constant stands for the prologue).
 void rt_split_plan(const cb_ctx* ctx, int m, int w, int* P, int* tiles_per_split) {
     const int ntiles = cb_div_up(m, kRtTileN);
     const int groups = cb_div_up(w, kHT * kRtTileM);
-    int p = max(1, ctx->sm_count / groups);  // one CTA per SM (TMEM: 512 columns each)
-    p = min(p, ntiles);
-    const int tps = cb_div_up(ntiles, p);
+    int best_p = 1;
+    double best_cost = 1e300;
+    for (int p = 1; p <= min(ntiles, 32); ++p) {
+        const int tps = cb_div_up(ntiles, p);
+        const int pp = cb_div_up(ntiles, tps);
+        const int rounds = cb_div_up(groups * pp, ctx->sm_count);
+        const double cost = rounds * (tps + 2.0);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best_p = p; }
+    }
+    const int tps = cb_div_up(ntiles, best_p);
     *tiles_per_split = tps;
     *P = cb_div_up(ntiles, tps);
 }
 
 }  // namespace
-
-int ransac_tc_max_splits(const cb_ctx* ctx, int m, int w) {
-    int P, tps;
-    rt_split_plan(ctx, m, w, &P, &tps);
-    return P;
-}
 
 int ransac_tc_pack_corr_launch(cb_ctx* ctx, const float4* src4, const float4* tgt4, int m, RansacState* state,
                                __nv_bfloat16* Bpack, cudaStream_t st) {
@@ -374,12 +380,10 @@ int ransac_tc_pack_corr_launch(cb_ctx* ctx, const float4* src4, const float4* tg
 
 int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_bfloat16* Bpack, const float* band,
                            const double* Tw, const float4* src4, const float4* tgt4, int m, int h0, int w,
-                           double thr2, const RansacState* state, int32_t* pc, double* ps, int* P_out,
-                           cudaStream_t st) {
+                           double thr2, const RansacState* state, int32_t* pc, double* ps, cudaStream_t st) {
     if (m >= (1 << 24)) CB_FAIL(ctx, CB_EUNSUPPORTED, "tensor-core RANSAC scoring holds at most 2^24 correspondences");
     int P, tps;
     rt_split_plan(ctx, m, w, &P, &tps);
-    *P_out = P;
     float* dump = ctx->ransac_dump;
     const int dump_ld = ctx->ransac_dump_ld;
     cudaError_t e;
