@@ -202,4 +202,15 @@ def get_context(device=None):
         cache = _tls.ctx = {}
     if device not in cache:
         cache[device] = Context(device)
+        with _lib_lock:
+            _all_contexts.append(cache[device])
     return cache[device]
+
+
+_all_contexts = []
+
+
+def all_contexts():
+    """Every thread-local context created so far (bench.py sums their launch counters)."""
+    with _lib_lock:
+        return list(_all_contexts)

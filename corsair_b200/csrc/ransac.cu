@@ -17,6 +17,7 @@
 #include "ransac_internal.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 // -------------------------------------------------------------------------- pack
 __global__ void ransac_pack_kernel(const float* __restrict__ src_xyz, const float* __restrict__ tgt_xyz,
@@ -581,7 +582,15 @@ __global__ void ransac_expand_T_kernel(const double* __restrict__ Tw, int h, dou
 // Waves of hypotheses: a small first wave (most adaptive runs stop inside it), then waves that give
 // every SM one 256-hypothesis CTA of the tensor-core scoring kernel.
 constexpr int kWaveFirst = 4096;
-static int ransac_wave_max(const cb_ctx* ctx) { return max(kWaveFirst, min(ctx->sm_count, 160) * 256); }
+static int ransac_wave_max(const cb_ctx* ctx) {
+    static int override_ctas = -1;  // CB_RANSAC_WAVE_CTAS: tuning knob (CTAs of 256 hypotheses per wave)
+    if (override_ctas < 0) {
+        const char* e = getenv("CB_RANSAC_WAVE_CTAS");
+        override_ctas = e ? atoi(e) : 0;
+    }
+    const int ctas = override_ctas > 0 ? min(override_ctas, 160) : min(ctx->sm_count, 160);
+    return max(kWaveFirst, ctas * 256);
+}
 static int ransac_wave_size(const cb_ctx* ctx, int wave_index) {
     return wave_index == 0 ? kWaveFirst : ransac_wave_max(ctx);
 }

@@ -12,11 +12,12 @@
 // expression on the raw float32 points, so the COUNT is exactly the float64 count; everything
 // outside the band (> 99.9 %) is decided by the tensor-core value alone.
 //
-// CTA = 256 hypotheses (two A tiles) x one split of the correspondences, 320 threads:
-//   warp 8  producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
-//   warp 9  one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
+// CTA = 256 hypotheses (two A tiles) x one split of the correspondences, 576 threads:
+//   warp 16 producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
+//   warp 17 one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
 //           a double-buffered TMEM accumulator (2 stages x 2 A tiles x 128 columns = 512)
-//   warps 0-7 epilogue: warp w reads lane quadrant w%4 of A tile w/4, 32 columns per tcgen05.ld
+//   warps 0-15 epilogue: warp w reads lane quadrant w%4 of A tile (w/4)%2, column half w/8; two
+//           32-column tcgen05.ld per tile, the second in flight while the first is processed
 #include "ransac_internal.cuh"
 
 #include <math.h>
@@ -25,7 +26,9 @@ namespace {
 
 constexpr int kHT = 2;            // A tiles (of 128 hypotheses) per CTA
 constexpr int kStages = 3;        // shared-memory ring of B tiles
-constexpr int kThreads = 320;
+constexpr int kEpiWarps = 16;     // 4 lane quadrants x 2 A tiles x 2 column halves
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = kEpiThreads + 64;  // + producer warp + MMA warp
 constexpr int kListCap = 4096;    // queued in-band evaluations per CTA (overflow is settled inline)
 constexpr int kListDrain = 2048;  // drain the queue at the next tile boundary once it holds this many
 constexpr uint32_t kATileBytes = kRtTileM * kRtKP * 2;  // 24 KB
@@ -156,12 +159,12 @@ __device__ __noinline__ void rt_overflow(int col, float u, const double* __restr
     dsum += ds;
 }
 
-// all 256 epilogue threads: re-decide the queued evaluations exactly, corrections into s_dcnt/s_dsum
+// all epilogue threads: re-decide the queued evaluations exactly, corrections into s_dcnt/s_dsum
 __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s_dcnt, double* s_dsum, int jcta, int w,
                                          const double* __restrict__ Tw, const float4* __restrict__ src4,
                                          const float4* __restrict__ tgt4, double thr2d) {
     const int nlist = min(*(volatile int*)&ctl->list_n, kListCap);
-    for (int i = threadIdx.x; i < nlist; i += 256) {
+    for (int i = threadIdx.x; i < nlist; i += kEpiThreads) {
         const int2 en = list[i];
         const int row = (en.x >> 24) & 0xff, col = en.x & 0xffffff;
         double dc, ds;
@@ -201,19 +204,19 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         }
         for (int i = 0; i < 2; ++i) {
             tc::mbar_init(&ctl->tmem_full[i], 1);
-            tc::mbar_init(&ctl->tmem_empty[i], 8);
+            tc::mbar_init(&ctl->tmem_empty[i], kEpiWarps);
         }
         ctl->list_n = 0;
         tc::fence_barrier_init();
     }
     if (threadIdx.x < kHT * kRtTileM) { s_dsum[threadIdx.x] = 0.0; s_dcnt[threadIdx.x] = 0.0; }
-    if (warp == 8) tc::tmem_alloc(&ctl->tmem_base, 512);
+    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 512);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tbase = ctl->tmem_base;
 
-    if (warp == 8) {
+    if (warp == kEpiWarps) {
         // ===== producer =====
         if (lane == 0) {
             tc::mbar_arrive_expect_tx(&ctl->a_full, kHT * kATileBytes);
@@ -227,7 +230,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                              kBTileBytes, &ctl->full[st]);
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == kEpiWarps + 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
             constexpr uint32_t idesc = tc::idesc_bf16(kRtTileM, kRtTileN);
@@ -255,62 +258,70 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             }
         }
     } else {
-        // ===== epilogue: 256 threads, one hypothesis each =====
-        const int a = warp >> 2;                           // A tile of this warp
+        // ===== epilogue: 512 threads; a hypothesis row is shared by two threads (column halves) =====
+        const int a = (warp >> 2) & 1;                     // A tile of this warp
+        const int half = warp >> 3;                        // columns [64*half, 64*half + 64) of every tile
         const int rloc = a * kRtTileM + (warp & 3) * 32 + lane;  // row inside the CTA
         const int j = jcta + rloc;                         // wave-relative hypothesis
         const bool valid = j < w;
         const float band = valid ? band_g[j] : -1.f;
         const double* Tj = Tw + (size_t)min(j, w - 1) * 12;
-        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN;
+        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN + half * 64;
         double cnt_d = 0.0, sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
-        for (int it = 0; it < ntiles; ++it) {
-            const int ts = it & 1, tuse = it >> 1;
-            tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
-            tc::fence_after_sync();
-            const int col0 = (t0 + it) * kRtTileN;
-            f32x2 c2 = pk2(0.f, 0.f), s2 = pk2(0.f, 0.f);
-#pragma unroll 1
-            for (int cb = 0; cb < kRtTileN / 32; ++cb) {
-                float v[32];
-                tc::tmem_ld32(lane_addr + ts * (kHT * kRtTileN) + cb * 32, v);
-                tc::tmem_ld_wait();
-                float bm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+        f32x2 c2, s2;
+        // one 32-column chunk: gate, count, sum, and the in-band test
+        auto process = [&](const float (&v)[32], int colc) {
+            float bm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
 #pragma unroll
-                for (int e = 0; e < 32; e += 2) {
-                    const float g0 = rt_gate(v[e]), g1 = rt_gate(v[e + 1]);
-                    const f32x2 g = pk2(g0, g1);
-                    c2 = add2(c2, g);
-                    s2 = fma2(g, pk2(v[e], v[e + 1]), s2);
-                    bm[e >> 3] = fminf(bm[e >> 3], fminf(fabsf(v[e]), fabsf(v[e + 1])));
-                }
-                if (DUMP) {
-                    if (valid)
-                        for (int e = 0; e < 32; ++e)
-                            if (col0 + cb * 32 + e < m) dump[(size_t)j * dump_ld + col0 + cb * 32 + e] = v[e];
-                }
-                if (fminf(fminf(bm[0], bm[1]), fminf(bm[2], bm[3])) <= band) {
+            for (int e = 0; e < 32; e += 2) {
+                const float g0 = rt_gate(v[e]), g1 = rt_gate(v[e + 1]);
+                const f32x2 g = pk2(g0, g1);
+                c2 = add2(c2, g);
+                s2 = fma2(g, pk2(v[e], v[e + 1]), s2);
+                bm[e >> 3] = fminf(bm[e >> 3], fminf(fabsf(v[e]), fabsf(v[e + 1])));
+            }
+            if (DUMP) {
+                if (valid)
+                    for (int e = 0; e < 32; ++e)
+                        if (colc + e < m) dump[(size_t)j * dump_ld + colc + e] = v[e];
+            }
+            if (fminf(fminf(bm[0], bm[1]), fminf(bm[2], bm[3])) <= band) {
 #pragma unroll
-                    for (int g8 = 0; g8 < 4; ++g8) {
-                        if (bm[g8] <= band) {
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    if (bm[g8] <= band) {
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                const float u = v[g8 * 8 + e];
-                                if (fabsf(u) <= band) {
-                                    const int col = col0 + cb * 32 + g8 * 8 + e;
-                                    const int pos = atomicAdd(&ctl->list_n, 1);
-                                    if (pos < kListCap) list[pos] = make_int2((rloc << 24) | col, __float_as_int(u));
-                                    else rt_overflow(col, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
-                                }
+                        for (int e = 0; e < 8; ++e) {
+                            const float u = v[g8 * 8 + e];
+                            if (fabsf(u) <= band) {
+                                const int col = colc + g8 * 8 + e;
+                                const int pos = atomicAdd(&ctl->list_n, 1);
+                                if (pos < kListCap) list[pos] = make_int2((rloc << 24) | col, __float_as_int(u));
+                                else rt_overflow(col, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
                             }
                         }
                     }
                 }
             }
-            // accumulator stage drained: hand it back to the MMA warp
+        };
+        for (int it = 0; it < ntiles; ++it) {
+            const int ts = it & 1, tuse = it >> 1;
+            tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
+            tc::fence_after_sync();
+            const int col0 = (t0 + it) * kRtTileN + half * 64;
+            const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
+            c2 = pk2(0.f, 0.f);
+            s2 = pk2(0.f, 0.f);
+            float v0[32], v1[32];
+            tc::tmem_ld32(taddr, v0);
+            tc::tmem_ld_wait();
+            tc::tmem_ld32(taddr + 32, v1);  // in flight while the first chunk is processed
+            process(v0, col0);
+            tc::tmem_ld_wait();
+            // accumulator stage drained (all of this warp's columns are in registers)
             tc::fence_before_sync();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
+            process(v1, col0 + 32);
             float x, y;
             unpk2(c2, x, y);
             cnt_d += (double)x + (double)y;
@@ -318,30 +329,31 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             sum_d += (double)x + (double)y;
             // every 16 tiles: if the queue is half full (a CTA-uniform decision) drain it
             if ((it & 15) != 15) continue;
-            named_bar_sync(1, 256);
+            named_bar_sync(1, kEpiThreads);
             if (*(volatile int*)&ctl->list_n >= kListDrain) {
                 rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
-                named_bar_sync(1, 256);
+                named_bar_sync(1, kEpiThreads);
                 if (threadIdx.x == 0) ctl->list_n = 0;
-                named_bar_sync(1, 256);
+                named_bar_sync(1, kEpiThreads);
             }
         }
         // settle the queued in-band evaluations of the whole CTA
-        named_bar_sync(1, 256);
+        named_bar_sync(1, kEpiThreads);
         rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
-        named_bar_sync(1, 256);
+        named_bar_sync(1, kEpiThreads);
         if (valid) {
-            const double c = cnt_d + dcnt + s_dcnt[rloc];
+            // this thread's share of the row; the queue's corrections ride with the first half
+            const double c = cnt_d + dcnt + (half == 0 ? s_dcnt[rloc] : 0.0);
             const long long ci = llrint(c);
-            // totals over the correspondence splits (zeroed by the fit kernel)
+            // totals over column halves and correspondence splits (zeroed by the fit kernel)
             atomicAdd(&pc[j], (int)ci);
             // sum of squared inlier distances = sum (d^2 - thr^2) + count * thr^2
-            atomicAdd(&ps[j], sum_d + dsum + s_dsum[rloc] + (double)ci * thr2d);
+            atomicAdd(&ps[j], sum_d + dsum + (half == 0 ? s_dsum[rloc] : 0.0) + (double)ci * thr2d);
         }
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 8) tc::tmem_dealloc(tbase, 512);
+    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, 512);
 }
 
 constexpr size_t kScoreSmem = kHT * kATileBytes + kStages * kBTileBytes + kListCap * sizeof(int2) +

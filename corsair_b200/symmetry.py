@@ -83,11 +83,12 @@ def select_cut(stats):
     return win
 
 
-def _masks_device(feat_d, xyz_d, K, max_sample, ctx):
+def _masks_device(feat_d, xyz_d, K, max_sample, ctx, rng=None):
     if K not in (2, 4):
         raise ValueError("not defined")
     n = xyz_d.shape[0]
-    random_points = np.random.choice(n, max_sample, replace=False)  # global RNG, utils/symmetry.py:193
+    # global RNG like utils/symmetry.py:193 unless the caller hands in its own RandomState
+    random_points = (rng or np.random).choice(n, max_sample, replace=False)
     centers, stats, _ = cut_model_device(feat_d, xyz_d, K, random_points, ctx)
     win = select_cut(stats.cpu().numpy())
     if win < 0:
@@ -143,8 +144,12 @@ def _pairing_ransac(ctx, F0s, A_perm, q_off, posF_d, B_parts, xyz0_d, xyz1_d, k_
 
 
 def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *, n_hypotheses=100000,
-             adaptive=True):
+             adaptive=True, rng=None):
     """utils/symmetry.py:262-358: pose with and without the symmetry-aided pairing search.
+
+    ``rng``: a ``np.random.RandomState`` for the segmentation's seed points instead of the global
+    NumPy RNG the reference draws from (``RandomState(s)`` gives the stream of ``np.random.seed(s)``);
+    needed when pairs are registered concurrently (sym_pose_many).
 
     Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success)."""
     ctx = _capi.get_context()
@@ -177,8 +182,8 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
 
     try:
         K = 4 if pos_sym >= 2 else 2
-        base_masks = _masks_device(baseF_d, xyz0_d, K, 100, ctx)
-        pos_masks = _masks_device(posF_d, xyz1_d, K, 100, ctx)
+        base_masks = _masks_device(baseF_d, xyz0_d, K, 100, ctx, rng)
+        pos_masks = _masks_device(posF_d, xyz1_d, K, 100, ctx, rng)
     except Exception as e:  # same swallow-and-fallback as utils/symmetry.py:299-301
         tqdm.write(f"symmetry failed use ransac: {e}")
         T_r, ch_r = cands[0]
@@ -209,3 +214,45 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     T_ransac = cands[0][0].cpu()
     T_best = cands[best][0].cpu()
     return T_best, float(chamf[best]), T_ransac, float(chamf[0]), True
+
+
+# ---------------------------------------------------------------------------------------------
+# Concurrent driver.  The reference registers its pairs one after the other (evaluation.py:297)
+# or under tqdm's thread_map (evaluation-shapenet.py:341); pairs are independent, and one pair's
+# chain of small dependent kernels (fit, fold, k-means: a handful of blocks each) cannot fill 148
+# SMs, so the drop-in offers the same loop on a few host threads, each with its own cb_ctx and
+# CUDA stream: the device overlaps one pair's latency-bound kernels with another pair's scoring.
+_pool = None
+_pool_workers = 0
+_worker_tls = __import__("threading").local()
+
+
+def _worker_run(device, ready, args, kwargs):
+    torch.cuda.set_device(device)
+    st = getattr(_worker_tls, "stream", None)
+    if st is None:
+        st = _worker_tls.stream = torch.cuda.Stream(device=device)
+    with torch.cuda.stream(st):
+        st.wait_event(ready)  # inputs were produced on the caller's stream
+        return sym_pose(*args, **kwargs)  # ends with its own device->host reads (stream-synchronised)
+
+
+def sym_pose_many(jobs, workers=4):
+    """Register independent pairs concurrently.  ``jobs``: iterable of ``(args, kwargs)`` for
+    sym_pose (pass ``rng=np.random.RandomState(seed)`` in kwargs for reproducible segmentations);
+    returns sym_pose's result tuples in job order.  ``workers <= 1`` runs them in the calling thread."""
+    global _pool, _pool_workers
+    jobs = list(jobs)
+    if workers <= 1 or len(jobs) <= 1:
+        return [sym_pose(*a, **k) for a, k in jobs]
+    if _pool is None or _pool_workers != workers:
+        from concurrent.futures import ThreadPoolExecutor
+        if _pool is not None:
+            _pool.shutdown(wait=True)
+        _pool = ThreadPoolExecutor(max_workers=workers, thread_name_prefix="corsair_b200")
+        _pool_workers = workers
+    device = torch.cuda.current_device()
+    ready = torch.cuda.Event()
+    ready.record(torch.cuda.current_stream(device))
+    futs = [_pool.submit(_worker_run, device, ready, a, k) for a, k in jobs]
+    return [f.result() for f in futs]

@@ -133,3 +133,20 @@ def test_irls_pose(ctx, rng):
     torch.testing.assert_close(corr.cpu(), rcorr, rtol=1e-5, atol=1e-5)
     torch.testing.assert_close(wt, rwt, rtol=1e-5, atol=1e-6)
     assert torch.allclose(tr, rtr, atol=1e-4)
+
+
+def test_sym_pose_many_matches_sequential(ctx):
+    """The threaded driver (own context + stream per host thread) returns exactly what the
+    sequential loop returns, in job order."""
+    from corsair_b200 import symmetry, synth
+    pairs = [synth.make_pair(200 + i, 32, "chair", n_raw=3000) for i in range(5)]
+    def jobs():
+        return [((p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"]),
+                 dict(k_nn=5, max_corr=0.2, seed=3, rng=np.random.RandomState(3), n_hypotheses=20000)) for p in pairs]
+    seq = symmetry.sym_pose_many(jobs(), workers=1)
+    par = symmetry.sym_pose_many(jobs(), workers=3)
+    par2 = symmetry.sym_pose_many(jobs(), workers=3)
+    for a, b, c in zip(seq, par, par2):
+        for x in (b, c):
+            assert np.array_equal(a[0].numpy(), x[0].numpy()) and np.array_equal(a[2].numpy(), x[2].numpy())
+            assert a[1] == x[1] and a[3] == x[3] and a[4] == x[4]
