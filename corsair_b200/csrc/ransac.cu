@@ -435,16 +435,21 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
         dev_work[CB_T_RANSAC_SCORE] += (double)w * (double)m * 32.0;  // bytes this wave streamed
         s_stop = h0 + w;
     }
-    // 1. totals (coalesced)
-    for (int j = tid; j < w; j += kFoldThreads) {
-        int cnt = 0;
-        double sm = 0.0;
-        for (int p = 0; p < P; ++p) {
-            cnt += pc[(size_t)p * w + j];
-            sm += ps[(size_t)p * w + j];
+    // 1. totals into shared memory (independent loads, unrolled so they overlap)
+    if (P == 1) {
+#pragma unroll 8
+        for (int j = tid; j < w; j += kFoldThreads) s_cnt[j] = pc[j];
+    } else {
+        for (int j = tid; j < w; j += kFoldThreads) {
+            int cnt = 0;
+            double sm = 0.0;
+            for (int p = 0; p < P; ++p) {
+                cnt += pc[(size_t)p * w + j];
+                sm += ps[(size_t)p * w + j];
+            }
+            s_cnt[j] = cnt;
+            ps[j] = sm;
         }
-        s_cnt[j] = cnt;
-        if (P > 1) ps[j] = sm;
     }
     __syncthreads();
     // 2. best count before each segment
@@ -461,8 +466,12 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
         __syncthreads();
     }
     int run = max(prev_count, tid > 0 ? s_scan[tid - 1] : 0);
-    // 3. first h at or beyond the (shrinking) budget
-    if (j0 < j1) {
+    // 3. first h at or beyond the (shrinking) budget.  The budget is non-increasing in the best
+    //    count, so if even the wave's highest count leaves it at or beyond the end of the wave nobody
+    //    stops inside (the usual case of a long run): skip the per-thread walks and their pow/log.
+    const int wave_max = max(prev_count, s_scan[kFoldThreads - 1]);
+    const int b_min = adaptive ? min(budget_in, ransac_budget_from_count(wave_max, m, ransac_n, conf, budget_in)) : budget_in;
+    if (b_min < h0 + w && j0 < j1) {
         int b = adaptive ? min(budget_in, ransac_budget_from_count(run, m, ransac_n, conf, budget_in)) : budget_in;
         int stop = -1;
         for (int j = j0; j < j1; ++j) {
@@ -514,11 +523,14 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
             __syncthreads();
             if (nxt == 0x7fffffff) break;
             last = nxt;
-            const double* Tj = Tw + (size_t)nxt * 12;
+            double Tj[12];
+#pragma unroll
+            for (int t = 0; t < 12; ++t) Tj[t] = Tw[(size_t)nxt * 12 + t];
             double sm = 0.0;
             int cn = 0;
+#pragma unroll 4
             for (int i = tid; i < m; i += kFoldThreads) {
-                const double dd = ransac_exact_d2(Tj, src4[i], tgt4[i]);
+                const double dd = ransac_exact_d2_inl(Tj, src4[i], tgt4[i]);
                 if (dd < thr2d) { sm += dd; ++cn; }
             }
             for (int o = 16; o > 0; o >>= 1) {

@@ -12,12 +12,12 @@
 // expression on the raw float32 points, so the COUNT is exactly the float64 count; everything
 // outside the band (> 99.9 %) is decided by the tensor-core value alone.
 //
-// CTA = 256 hypotheses (two A tiles) x one split of the correspondences, 576 threads:
-//   warp 16 producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
-//   warp 17 one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
+// CTA = 256 hypotheses (two A tiles) x one split of the correspondences, 320 threads:
+//   warp 8  producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
+//   warp 9  one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
 //           a double-buffered TMEM accumulator (2 stages x 2 A tiles x 128 columns = 512)
-//   warps 0-15 epilogue: warp w reads lane quadrant w%4 of A tile (w/4)%2, column half w/8; two
-//           32-column tcgen05.ld per tile, the second in flight while the first is processed
+//   warps 0-7 epilogue: warp w reads lane quadrant w%4 of A tile w/4 in 32-column tcgen05.ld.
+//           The kernel is bound by this drain: tensor memory reads at 64 B/clk/SM = 16 evaluations/clk/SM
 #include "ransac_internal.cuh"
 
 #include <math.h>
@@ -26,7 +26,10 @@ namespace {
 
 constexpr int kHT = 2;            // A tiles (of 128 hypotheses) per CTA
 constexpr int kStages = 3;        // shared-memory ring of B tiles
-constexpr int kEpiWarps = 16;     // 4 lane quadrants x 2 A tiles x 2 column halves
+constexpr int kEpiWarps = 8;      // 4 lane quadrants x 2 A tiles x kColSplit column parts
+constexpr int kColSplit = kEpiWarps / 8;
+constexpr int kColsPerThread = kRtTileN / kColSplit;
+constexpr int kChunks = kColsPerThread / 32;  // 32-column tcgen05.ld per thread and tile (even)
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = kEpiThreads + 64;  // + producer warp + MMA warp
 constexpr int kListCap = 4096;    // queued in-band evaluations per CTA (overflow is settled inline)
@@ -258,15 +261,15 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             }
         }
     } else {
-        // ===== epilogue: 512 threads; a hypothesis row is shared by two threads (column halves) =====
+        // ===== epilogue: one thread per hypothesis row and column part =====
         const int a = (warp >> 2) & 1;                     // A tile of this warp
-        const int half = warp >> 3;                        // columns [64*half, 64*half + 64) of every tile
+        const int half = warp >> 3;                        // column part of every tile this warp drains
         const int rloc = a * kRtTileM + (warp & 3) * 32 + lane;  // row inside the CTA
         const int j = jcta + rloc;                         // wave-relative hypothesis
         const bool valid = j < w;
         const float band = valid ? band_g[j] : -1.f;
         const double* Tj = Tw + (size_t)min(j, w - 1) * 12;
-        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN + half * 64;
+        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN + half * kColsPerThread;
         double cnt_d = 0.0, sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
         f32x2 c2, s2;
         // one 32-column chunk: gate, count, sum, and the in-band test
@@ -307,21 +310,23 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             const int ts = it & 1, tuse = it >> 1;
             tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
             tc::fence_after_sync();
-            const int col0 = (t0 + it) * kRtTileN + half * 64;
+            const int col0 = (t0 + it) * kRtTileN + half * kColsPerThread;
             const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
             c2 = pk2(0.f, 0.f);
             s2 = pk2(0.f, 0.f);
-            float v0[32], v1[32];
-            tc::tmem_ld32(taddr, v0);
-            tc::tmem_ld_wait();
-            tc::tmem_ld32(taddr + 32, v1);  // in flight while the first chunk is processed
-            process(v0, col0);
-            tc::tmem_ld_wait();
-            // accumulator stage drained (all of this warp's columns are in registers)
+            // drain this thread's columns, 32 at a time (measured: neither double-buffering the loads
+            // nor 16 epilogue warps beats this; the tensor-memory read rate is the limit)
+#pragma unroll 1
+            for (int k = 0; k < kChunks; ++k) {
+                float v[32];
+                tc::tmem_ld32(taddr + k * 32, v);
+                tc::tmem_ld_wait();
+                process(v, col0 + k * 32);
+            }
+            // accumulator stage drained: hand it back to the MMA warp
             tc::fence_before_sync();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
-            process(v1, col0 + 32);
             float x, y;
             unpk2(c2, x, y);
             cnt_d += (double)x + (double)y;
