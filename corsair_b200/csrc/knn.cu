@@ -12,6 +12,7 @@
 //   4. fallback: queued rows are solved by exact float64 brute force.
 // Engine E2 (anything else): exact float64 distance rows + per-row radix select (select.cu).
 #include "common.cuh"
+#include <stdlib.h>
 #include "knn_internal.cuh"
 
 #include <float.h>
@@ -138,11 +139,14 @@ __device__ __forceinline__ float knn_out_dist(double key, int metric) {
     return (float)key;
 }
 
-// one warp per query; ncand = S*KC <= 128 candidates (<= 4 per lane)
+// one warp per query; ncand = S*KC <= 256 candidate slots (<= 8 per lane; unused slots hold -1).
+// bound (optional, [nq, S]): per chunk a score no dropped reference of that chunk is below;
+// without it the chunk's last (worst kept) candidate score plays that role.
 __global__ void __launch_bounds__(256)
 knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int d, int dq_stride,
                   int k, int metric, const int32_t* __restrict__ cand_idx, const float* __restrict__ cand_s,
-                  int S, int KC, const unsigned int* __restrict__ rmax_bits, double gamma,
+                  int S, int KC, const float* __restrict__ bound, const unsigned int* __restrict__ rmax_bits,
+                  double gamma,
                   int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist,
                   int32_t* __restrict__ fb_list, int* __restrict__ fb_count) {
     const int lane = threadIdx.x & 31;
@@ -151,10 +155,11 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int ncand = S * KC;
     const float* qp = q + (size_t)qi * dq_stride;
-    double key[4];
-    int id[4];
+    constexpr int SL = 8;
+    double key[SL];
+    int id[SL];
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < SL; ++t) {
         int ci = lane + 32 * t;
         id[t] = -1;
         key[t] = INFINITY;
@@ -172,7 +177,7 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
         double bk = INFINITY;
         int bj = 0x7fffffff, bt = -1;
 #pragma unroll
-        for (int t = 0; t < 4; ++t)
+        for (int t = 0; t < SL; ++t)
             if (id[t] >= 0 && knn_less(key[t], id[t], bk, bj)) { bk = key[t]; bj = id[t]; bt = t; }
         double wk = bk;
         int wj = bj;
@@ -184,7 +189,7 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
         if (wj == 0x7fffffff) break;  // fewer than k candidates (cannot happen when k <= nr)
         if (bt >= 0 && bj == wj) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
+            for (int t = 0; t < SL; ++t)
                 if (t == bt) id[t] = -1;
         }
         if (lane == 0) {
@@ -211,7 +216,7 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
     }
     bool bad = found < k;
     for (int c = lane; c < S; c += 32) {
-        float w = cand_s[((size_t)qi * S + c) * KC + KC - 1];
+        float w = bound ? bound[(size_t)qi * S + c] : cand_s[((size_t)qi * S + c) * KC + KC - 1];
         if (!(w == INFINITY) && !((double)w - e + shift > kth)) bad = true;
     }
     bad = __any_sync(0xffffffffu, bad);
@@ -294,10 +299,16 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     }
     const int dp = d <= 16 ? 16 : 32;
     const int KC = k <= 5 ? 8 : 16;
-    // reference chunks: enough blocks for >= 2 waves, chunks of >= 256 refs, S*KC <= 128
+    // the tcgen05 variant collects every reference at or above a per-(query, chunk) threshold: up to
+    // LC = 3 KC list slots per chunk; the SIMT variant keeps exactly the KC best
+    const bool use_tc = ctx->knn_variant != 1;
+    const int LC = use_tc ? 3 * KC : KC;
+    // reference chunks: about one CTA per SM, chunks of whole 256-reference tiles, S*LC <= 256
+    static int waves_x2 = -1;  // CB_KNN_HALFWAVES: tuning knob, CTAs per SM x 2 the chunking aims at
+    if (waves_x2 < 0) { const char* e = getenv("CB_KNN_HALFWAVES"); waves_x2 = e ? atoi(e) : 2; }
     int qblocks = cb_div_up(nq, 128);
-    int S = cb_div_up(2 * ctx->sm_count, qblocks);
-    S = max(1, min(S, 128 / KC));
+    int S = (waves_x2 * ctx->sm_count / 2) / qblocks;  // rounded down: no second round of CTAs
+    S = max(1, min(S, 256 / LC));
     S = min(S, max(1, nr / 256));
     int chunk = cb_div_up(nr, S);
     chunk = (chunk + 255) & ~255;  // whole tensor-core column tiles (256 references) per chunk
@@ -318,10 +329,11 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     }
     float* rn = cb_alloc_t<float>(ctx, nr);
     unsigned int* scal = cb_alloc_t<unsigned int>(ctx, 2);  // [0] rmax bits, [1] fallback count
-    int32_t* ci = cb_alloc_t<int32_t>(ctx, (size_t)nq * S * KC);
-    float* cs = cb_alloc_t<float>(ctx, (size_t)nq * S * KC);
+    int32_t* ci = cb_alloc_t<int32_t>(ctx, (size_t)nq * S * LC);
+    float* cs = cb_alloc_t<float>(ctx, (size_t)nq * S * LC);
+    float* bound = cb_alloc_t<float>(ctx, (size_t)nq * S);
     int32_t* fb = cb_alloc_t<int32_t>(ctx, nq);
-    if (!rn || !scal || !ci || !cs || !fb) return CB_ENOMEM;
+    if (!rn || !scal || !ci || !cs || !bound || !fb) return CB_ENOMEM;
     CB_CUDA(ctx, cudaMemsetAsync(scal, 0, 2 * sizeof(unsigned int), st));
     ctx->knn_fb_count = (const int*)(scal + 1);
     knn_norms_kernel<<<cb_div_up(nr, 256), 256, 0, st>>>(rd, nr, dp, rn, scal);
@@ -329,19 +341,13 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
 
     const int maxdot = metric == CB_KNN_MAXDOT;
     double gamma = (dp + 4) * 6.0e-8;
-    bool done = false;
     {
     cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
-    if (ctx->knn_variant != 1) {
-        int rc = knn_cand_tc_launch(ctx, qd, nq, rd, rn, nr, dp, KC, chunk, S, maxdot, ci, cs, st);
-        if (rc == CB_OK) {
-            done = true;
-            gamma = knn_cand_tc_gamma(dp);
-        } else if (rc != CB_EUNSUPPORTED || ctx->knn_variant == 2) {
-            return rc;
-        }
-    }
-    if (!done) {
+    if (use_tc) {
+        int rc = knn_cand_tc_launch(ctx, qd, nq, rd, rn, nr, dp, KC, LC, chunk, S, maxdot, ci, cs, bound, st);
+        if (rc) return rc;
+        gamma = knn_cand_tc_gamma(dp);
+    } else {
         if (dp == 16 && KC == 8) launch_simt<16, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         else if (dp == 16) launch_simt<16, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         else if (KC == 8) launch_simt<32, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
@@ -350,8 +356,9 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     }
     }
     cb_timed_scope tscope2(ctx, CB_T_KNN_RERANK, 0.0, st);
-    knn_rerank_kernel<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, dp, k, metric, ci, cs, S, KC, scal, gamma,
-                                                       idx, idx32, dist, fb, (int*)(scal + 1));
+    knn_rerank_kernel<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, dp, k, metric, ci, cs, S, LC,
+                                                       use_tc ? bound : nullptr, scal, gamma, idx, idx32, dist, fb,
+                                                       (int*)(scal + 1));
     CB_LAUNCH_CHECK(ctx);
     knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, dp, k, metric, fb,
                                                                      (int*)(scal + 1), idx, idx32, dist);
@@ -364,7 +371,7 @@ static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
     size_t b = 0;
     b += cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nr * 32 * 4);  // pads
     b += cb_align((size_t)nr * 4) + 256;
-    b += 2 * cb_align((size_t)nq * 128 * 4) + cb_align((size_t)nq * 4);
+    b += 2 * cb_align((size_t)nq * 256 * 4) + cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nq * 4);
     b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + (1 << 16);  // packed bf16 operand tiles of the tc variant
     return b;
 }

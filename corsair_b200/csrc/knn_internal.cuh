@@ -3,14 +3,18 @@
 #include "common.cuh"
 
 // Candidate layout shared by both candidate variants: for query qi and reference chunk c
-// (references [c*chunk, min(nr,(c+1)*chunk))) the KC best approximate scores, ascending, at
-// cand_s[(qi*S + c)*KC + t] with their GLOBAL reference index in cand_idx (unused: -1 / +inf).
+// (references [c*chunk, min(nr,(c+1)*chunk))) LC list slots at cand_s[(qi*S + c)*LC + t] (approximate
+// scores, smaller is better) with their GLOBAL reference index in cand_idx (unused: -1 / +inf).
+// SIMT variant: LC = KC, the KC best in ascending order.
 
-// tcgen05 candidate pass (knn_tc.cu).  d in {16,32}.  Returns CB_EUNSUPPORTED when the shape is
-// outside what the tensor-core kernel covers (caller falls back to the SIMT kernel).
+// tcgen05 candidate pass (knn_tc.cu), d in {16,32}, KC in {8,16}, LC = 3 KC: every reference of the
+// chunk whose score is at or below the chunk's threshold (the KC-th best of its column-group minima,
+// so at least KC references qualify), in column order; bound[qi*S + c] = that threshold (no dropped
+// reference scores below it), -inf when more than LC qualified (the re-rank then sends the row to
+// the exact fallback).
 int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr,
-                       int d, int KC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s,
-                       cudaStream_t st);
+                       int d, int KC, int LC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s,
+                       float* bound, cudaStream_t st);
 // relative error bound of the tcgen05 split-bf16 inner product: |err| <= gamma * |q| |r|
 double knn_cand_tc_gamma(int d);
 

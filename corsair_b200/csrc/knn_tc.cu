@@ -14,8 +14,16 @@
 //   warp 4  producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
 //   warp 5  one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
 //           of two 256-column TMEM accumulators and commits to mbarriers
-//   warps 0-3 epilogue: tcgen05.ld 32 columns at a time, group-max filter against the row's
-//           current KC-th best, sorted insertion in registers; overlaps the next tile's MMAs.
+//   warps 0-3 epilogue: one query row (TMEM lane) per thread, tcgen05.ld 32 columns at a time.
+// The chunk's GEMM runs TWICE (the tensor pipe is nearly idle, the operands sit in L2):
+//   pass 1  per row, the maxima of column groups (16 or 8 columns) go through a branch-free
+//           sorted insertion into the row's KC best group maxima; their KC-th is the row's
+//           threshold tau: at least KC references of the chunk score at or above it
+//   pass 2  every reference with score >= tau is appended to the row's candidate list: a branch-free
+//           32-bit qualification mask per tcgen05.ld, then one short loop over its set bits.
+// A per-lane sorted top-k over all columns would make the warp take the insertion path whenever
+// ANY of its 32 rows inserts, i.e. for nearly every column of a cold list (measured: 1 400
+// instructions per 32 columns); the threshold form costs ~0.6 + ~4 instructions per element.
 #include "common.cuh"
 #include "knn_internal.cuh"
 #include "tc_common.cuh"
@@ -33,8 +41,12 @@ __host__ __device__ constexpr int kprime(int D) { return 3 * D + kExtraK; }
 
 // fp32 rows [n, D] -> packed bf16 operand tiles.  One thread per (row, 8-column group).
 // is_b: 0 = A layout (hi|hi|lo|ones), 1 = B layout (hi|lo|hi|-norm/2 split in three).
+// B rows are stored at the scrambled position (row * perm_a) mod n_pad (perm_a coprime to n_pad;
+// 1 for A): the column groups of the threshold pass then hold pseudo-random subsets of the
+// references, whatever spatial order (and feature similarity between neighbours) the cloud has.
 __global__ void knn_tc_pack_kernel(const float* __restrict__ x, const float* __restrict__ norms, int n, int n_pad,
-                                   int D, int TR, int is_b, int maxdot, __nv_bfloat16* __restrict__ out) {
+                                   int D, int TR, int is_b, int maxdot, unsigned perm_a,
+                                   __nv_bfloat16* __restrict__ out) {
     const int KP = kprime(D);
     const int groups = KP / 8;
     const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -65,7 +77,8 @@ __global__ void knn_tc_pack_kernel(const float* __restrict__ x, const float* __r
             v[0] = __float2bfloat16_rn(-1e30f);  // padding references can never enter a list
         }
     }
-    const int tile = row / TR, r = row % TR;
+    const int prow = (int)(((unsigned long long)row * perm_a) % (unsigned)n_pad);
+    const int tile = prow / TR, r = prow % TR;
     char* dst = reinterpret_cast<char*>(out) + (size_t)tile * TR * KP * 2 + tc::tile_offset(TR, r, kc);
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
 }
@@ -78,8 +91,11 @@ struct TcSmemCtl {
 template <int D, int KC>
 __global__ void __launch_bounds__(kThreads, 1)
 knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack, int nq, int nr,
-              int chunk, int S, int maxdot, int32_t* __restrict__ cand_idx, float* __restrict__ cand_s) {
+              int chunk, int S, int maxdot, unsigned perm_inv, int nr_pad, int32_t* __restrict__ cand_idx,
+              float* __restrict__ bound) {
     constexpr int KP = kprime(D);
+    constexpr int LC = 3 * KC;            // list slots per (query, chunk)
+    constexpr int GROUP = 128 / KC;       // columns per group maximum: 16 (KC = 8) or 8 (KC = 16)
     constexpr uint32_t A_BYTES = kTileM * KP * 2, B_BYTES = kTileN * KP * 2;
     constexpr uint32_t LBO_A = (kTileM / 8) * 128, LBO_B = (kTileN / 8) * 128;
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -91,6 +107,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
     const int t0 = (c * chunk) / kTileN;
     const int t1 = min((nr + kTileN - 1) / kTileN, ((c + 1) * chunk) / kTileN);
     const int ntiles = t1 - t0;
+    const int nsteps = 2 * ntiles;  // the chunk's tiles, twice
 
     if (threadIdx.x == 0) {
         tc::mbar_init(&ctl->a_full, 1);
@@ -113,11 +130,12 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
         if (lane == 0) {
             tc::mbar_arrive_expect_tx(&ctl->a_full, A_BYTES);
             tc::bulk_g2s(sA, reinterpret_cast<const char*>(Apack) + (size_t)blockIdx.x * A_BYTES, A_BYTES, &ctl->a_full);
-            for (int it = 0; it < ntiles; ++it) {
+            for (int it = 0; it < nsteps; ++it) {
                 const int st = it & 1, use = it >> 1;
+                const int tile = t0 + (it >= ntiles ? it - ntiles : it);
                 tc::mbar_wait(&ctl->empty[st], (use & 1) ^ 1);
                 tc::mbar_arrive_expect_tx(&ctl->full[st], B_BYTES);
-                tc::bulk_g2s(sB + st * B_BYTES, reinterpret_cast<const char*>(Bpack) + (size_t)(t0 + it) * B_BYTES, B_BYTES,
+                tc::bulk_g2s(sB + st * B_BYTES, reinterpret_cast<const char*>(Bpack) + (size_t)tile * B_BYTES, B_BYTES,
                              &ctl->full[st]);
             }
         }
@@ -127,7 +145,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             constexpr uint32_t idesc = tc::idesc_bf16(kTileM, kTileN);
             const uint32_t a_addr = tc::smem_u32(sA);
             tc::mbar_wait(&ctl->a_full, 0);
-            for (int it = 0; it < ntiles; ++it) {
+            for (int it = 0; it < nsteps; ++it) {
                 const int st = it & 1, use = it >> 1;
                 tc::mbar_wait(&ctl->full[st], use & 1);
                 tc::mbar_wait(&ctl->tmem_empty[st], (use & 1) ^ 1);
@@ -147,37 +165,52 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
         // ===== epilogue: 128 threads, one query row (TMEM lane) each =====
         const int row = threadIdx.x;
         const int qi = blockIdx.x * kTileM + row;
-        float bs[KC];
-        int bi[KC];
+        const size_t o = ((size_t)min(qi, nq - 1) * S + c) * LC;
+        const bool live = qi < nq;
+        float top[KC];  // the KC best group maxima, descending
 #pragma unroll
-        for (int t = 0; t < KC; ++t) { bs[t] = -INFINITY; bi[t] = -1; }
-        for (int it = 0; it < ntiles; ++it) {
+        for (int t = 0; t < KC; ++t) top[t] = -INFINITY;
+        float tau = -INFINITY;
+        int cnt = 0;
+        for (int it = 0; it < nsteps; ++it) {
             const int st = it & 1, use = it >> 1;
+            const bool second = it >= ntiles;
             tc::mbar_wait(&ctl->tmem_full[st], use & 1);
             tc::fence_after_sync();
-            const int col0 = (t0 + it) * kTileN;
+            const int col0 = (t0 + (second ? it - ntiles : it)) * kTileN;
+            if (it == ntiles) tau = fmaxf(top[KC - 1], -1e29f);  // padding (-1e30) never qualifies
 #pragma unroll 1
             for (int cb = 0; cb < kTileN / 32; ++cb) {
                 float v[32];
                 tc::tmem_ld32(tbase + ((uint32_t)(warp * 32) << 16) + st * kTileN + cb * 32, v);
                 tc::tmem_ld_wait();
-                float g = v[0];
+                if (!second) {
 #pragma unroll
-                for (int e = 1; e < 32; ++e) g = fmaxf(g, v[e]);
-                if (g > bs[KC - 1]) {
+                    for (int g = 0; g < 32 / GROUP; ++g) {
+                        float x = v[g * GROUP];
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        if (v[e] > bs[KC - 1]) {
-                            bs[KC - 1] = v[e];
-                            bi[KC - 1] = col0 + cb * 32 + e;
+                        for (int e = 1; e < GROUP; ++e) x = fmaxf(x, v[g * GROUP + e]);
+                        // branch-free insertion into the descending list (x sinks to its place)
 #pragma unroll
-                            for (int t = KC - 1; t > 0; --t) {
-                                if (bs[t] > bs[t - 1]) {
-                                    float fs = bs[t]; bs[t] = bs[t - 1]; bs[t - 1] = fs;
-                                    int fi = bi[t]; bi[t] = bi[t - 1]; bi[t - 1] = fi;
-                                }
-                            }
+                        for (int t = 0; t < KC; ++t) {
+                            const float hi = fmaxf(top[t], x);
+                            x = fminf(top[t], x);
+                            top[t] = hi;
                         }
+                    }
+                } else {
+                    // which of the 32 columns qualify: a bit mask (branch-free)
+                    unsigned mask = 0;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) mask |= (v[e] >= tau ? 1u : 0u) << e;
+                    // append their reference indices (the re-rank recomputes every candidate exactly,
+                    // the approximate scores are not needed); ~1 % of the columns qualify
+                    while (mask) {
+                        const int e = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        if (cnt < LC && live)
+                            cand_idx[o + cnt] = (int)(((unsigned long long)(col0 + cb * 32 + e) * perm_inv) % (unsigned)nr_pad);
+                        ++cnt;
                     }
                 }
             }
@@ -185,14 +218,10 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
         }
-        if (qi < nq) {
-            const size_t o = ((size_t)qi * S + c) * KC;
-#pragma unroll
-            for (int t = 0; t < KC; ++t) {
-                const bool ok = bi[t] >= 0 && bi[t] < nr;
-                cand_idx[o + t] = ok ? bi[t] : -1;
-                cand_s[o + t] = ok ? (maxdot ? -bs[t] : -2.f * bs[t]) : INFINITY;
-            }
+        if (live) {
+            for (int t = min(cnt, LC); t < LC; ++t) cand_idx[o + t] = -1;
+            // no dropped reference scores below the threshold; an overflowing list proves nothing
+            bound[(size_t)qi * S + c] = cnt > LC ? -INFINITY : (maxdot ? -tau : -2.f * tau);
         }
     }
     tc::fence_before_sync();
@@ -202,13 +231,13 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
 
 template <int D, int KC>
 cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
-                      int32_t* ci, float* cs, cudaStream_t st) {
+                      unsigned perm_inv, int nr_pad, int32_t* ci, float* bound, cudaStream_t st) {
     constexpr int KP = kprime(D);
     const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + sizeof(TcSmemCtl) + 64;
     cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((nq + kTileM - 1) / kTileM, S);
-    knn_tc_kernel<D, KC><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, ci, cs);
+    knn_tc_kernel<D, KC><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, ci, bound);
     return cudaGetLastError();
 }
 
@@ -221,25 +250,35 @@ extern "C" const char* cb_knn_variant(const cb_ctx* ctx) {
 }
 
 int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr, int d, int KC,
-                       int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s, cudaStream_t st) {
-    if ((d != 16 && d != 32) || (KC != 8 && KC != 16) || chunk % kTileN != 0) return CB_EUNSUPPORTED;
+                       int LC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s, float* bound,
+                       cudaStream_t st) {
+    if ((d != 16 && d != 32) || (KC != 8 && KC != 16) || LC != 3 * KC || chunk % kTileN != 0)
+        CB_FAIL(ctx, CB_EUNSUPPORTED, "knn_cand_tc_launch: unsupported shape (d=%d KC=%d LC=%d chunk=%d)", d, KC, LC, chunk);
     const int KP = kprime(d);
     const int nq_pad = cb_div_up(nq, kTileM) * kTileM, nr_pad = cb_div_up(nr, kTileN) * kTileN;
     __nv_bfloat16* A = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nq_pad * KP);
     __nv_bfloat16* B = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nr_pad * KP);
     if (!A || !B) return CB_ENOMEM;
     const int groups = KP / 8;
+    (void)cand_s;
+    // multiplicative scramble of the reference rows: perm_a ~ 0.618 n_pad, coprime to n_pad
+    unsigned perm_a = ((unsigned)(0.6180339887 * nr_pad)) | 1u, perm_inv = 1;
+    for (;; perm_a += 2) {
+        long long g0 = nr_pad, g1 = perm_a % (unsigned)nr_pad, x0 = 0, x1 = 1;  // extended Euclid
+        while (g1) { long long qq = g0 / g1, t = g0 - qq * g1; g0 = g1; g1 = t; t = x0 - qq * x1; x0 = x1; x1 = t; }
+        if (g0 == 1) { perm_inv = (unsigned)((x0 % nr_pad + nr_pad) % nr_pad); perm_a %= (unsigned)nr_pad; break; }
+    }
     knn_tc_pack_kernel<<<(unsigned)(((size_t)nq_pad * groups + 255) / 256), 256, 0, st>>>(q, nullptr, nq, nq_pad, d,
-                                                                                          kTileM, 0, maxdot, A);
+                                                                                          kTileM, 0, maxdot, 1u, A);
     CB_LAUNCH_CHECK(ctx);
     knn_tc_pack_kernel<<<(unsigned)(((size_t)nr_pad * groups + 255) / 256), 256, 0, st>>>(r, rn, nr, nr_pad, d, kTileN, 1,
-                                                                                          maxdot, B);
+                                                                                          maxdot, perm_a, B);
     CB_LAUNCH_CHECK(ctx);
     cudaError_t e;
-    if (d == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
-    else if (d == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
-    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
-    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, cand_s, st);
+    if (d == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    else if (d == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
     ctx->launches++;
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "knn_tc_kernel launch failed: %s", cudaGetErrorString(e));
     return CB_OK;
