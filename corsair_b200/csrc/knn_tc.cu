@@ -203,6 +203,9 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                     unsigned mask = 0;
 #pragma unroll
                     for (int e = 0; e < 32; ++e) mask |= (v[e] >= tau ? 1u : 0u) << e;
+                    // padding rows (all-equal scores) and rows whose list already overflowed (they go
+                    // to the exact fallback whatever else qualifies) must not spin in the loop below
+                    if (!live || cnt > LC) mask = 0;
                     // append their reference indices (the re-rank recomputes every candidate exactly,
                     // the approximate scores are not needed); ~1 % of the columns qualify
                     while (mask) {
