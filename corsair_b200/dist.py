@@ -40,6 +40,12 @@ def _all_gather(t):
     rank, ws = world()
     if ws == 1:
         return [t]
+    if t.is_cuda and dist.get_backend() == "gloo":
+        # ranks sharing one GPU in tests: gloo gathers through the host
+        host = t.detach().cpu().contiguous()
+        out = [torch.empty_like(host) for _ in range(ws)]
+        dist.all_gather(out, host)
+        return [o.to(t.device) for o in out]
     out = [torch.empty_like(t) for _ in range(ws)]
     dist.all_gather(out, t.contiguous())
     return out
@@ -87,3 +93,70 @@ def merge_best_hypothesis(T, stats, h_lo):
 def gather_rows(rows):
     """All-gather equally shaped per-rank result rows ([n_local, C]) -> [world*n_local, C]."""
     return torch.cat(_all_gather(rows), dim=0)
+
+
+# ---- the three exchanges of SURVEY.md section 8(e), end to end on the device kernels -------------
+def retrieval_topk_sharded(queries, library, k, metric="euclidean"):
+    """DB-sharded retrieval: `library` is the FULL [L, d] array (every rank slices its own
+    shard_range rows; pass a pre-sliced shard with `library=(shard, lo)`).  Per-shard top-k on the
+    device (cb_retrieval_topk), one all-gather of [Q, k] records, merge by (distance, global index).
+    Returns (idx [Q,k] int64, dist [Q,k] float64) NumPy, identical on every rank."""
+    from . import retrieval
+    if isinstance(library, tuple):
+        shard, lo = library
+    else:
+        lo, hi = shard_range(len(library))
+        shard = library[lo:hi]
+    kk = min(k, len(shard))
+    idx, d = retrieval.topk(queries, shard, kk, metric=metric)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    pad = k - kk  # a shard smaller than k contributes +inf fillers
+    ti = torch.from_numpy(np.pad(idx, ((0, 0), (0, pad)), constant_values=0)).to(dev)
+    td = torch.from_numpy(np.pad(d, ((0, 0), (0, pad)), constant_values=np.inf)).to(dev)
+    gi, gd = merge_topk(ti, td, lo, k)
+    return gi.cpu().numpy(), gd.cpu().numpy()
+
+
+def ransac_sharded(src_xyz, tgt_xyz, max_corr_dist, seed=0, n_hypotheses=4096, *, src_idx=None, tgt_idx=None):
+    """Hypothesis-sharded RANSAC with a fixed budget (BASELINE.json configs[4]): rank r scores
+    hypotheses [lo_r, hi_r) of the SAME seeded minimal-set stream (cb_draw_minimal_sets), the best
+    records are merged with Open3D's rule after one all-gather.  Returns (T [4,4] f64, stats [4] f64
+    = global best_h, inliers, sum_d2, n_evaluated) CUDA tensors, identical on every rank and equal to
+    the single-GPU result with adaptive=False."""
+    from . import _capi, eval_pose
+    ctx = _capi.get_context()
+    m = len(src_idx) if src_idx is not None else (len(tgt_idx) if tgt_idx is not None else len(src_xyz))
+    lo, hi = shard_range(int(n_hypotheses))
+    sets = ctx.empty((int(n_hypotheses), eval_pose.RANSAC_N), torch.int32)
+    ctx.call("cb_draw_minimal_sets", int(seed) & 0xFFFFFFFFFFFFFFFF, int(m), int(n_hypotheses), eval_pose.RANSAC_N,
+             _capi.ptr(sets), ctx.stream)
+    if hi > lo:
+        res = eval_pose.ransac_device(src_xyz, tgt_xyz, max_corr_dist, seed, src_idx=src_idx, tgt_idx=tgt_idx,
+                                      minimal_sets=sets[lo:hi].contiguous(), adaptive=False, ctx=ctx)
+        T, stats = res["T"], res["stats"]
+    else:
+        T = torch.eye(4, dtype=torch.float64, device=ctx.device)
+        stats = torch.tensor([-1.0, 0.0, 0.0, 0.0], dtype=torch.float64, device=ctx.device)
+    return merge_best_hypothesis(T, stats, lo)
+
+
+def chamfer_matrix_sharded(pcs):
+    """All-pairs Chamfer table (utils/pc_dist.py:61-99) with the rows split over ranks: every rank
+    computes its block of full rows on the device (cb_chamfer_matrix), one all-gather of the blocks
+    (padded to equal height).  Returns the [L,L] float64 table (diagonal 200 like the reference)."""
+    from . import pc_dist
+    L = len(pcs)
+    stack = torch.stack([p if isinstance(p, torch.Tensor) else torch.from_numpy(np.asarray(p)) for p in pcs]).float()
+    rank, ws = world()
+    lo, hi = shard_range(L)
+    rows = (L + ws - 1) // ws
+    dev = torch.device("cuda", torch.cuda.current_device())
+    block = torch.zeros((rows, L), dtype=torch.float64, device=dev)
+    if hi > lo:
+        block[:hi - lo] = pc_dist.chamfer_rows_device(stack, lo, hi)
+    allb = gather_rows(block).cpu().numpy()
+    out = np.empty((L, L), np.float64)
+    for r in range(ws):
+        a, b = shard_range(L, r, ws)
+        out[a:b] = allb[r * rows:r * rows + (b - a)]
+    return out
