@@ -624,10 +624,15 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
     constexpr int NP = 2;                   // hypothesis pairs per SIMT scoring thread
     const bool use_tc = ctx->ransac_variant != 1 && m < (1 << 24);
     const int m_pad = cb_div_up(max(m, 1), kRtTileN) * kRtTileN;
+    // tensor-core path: after the first wave ONE fit launch covers every remaining hypothesis (it
+    // fills the machine better than a fit per wave), so the per-hypothesis buffers span the whole run
+    const bool merged = use_tc && h_total > kWaveFirst && h_total <= (1 << 18);
+    const size_t hcap = merged ? (size_t)h_total : (size_t)wmax;
+    const size_t n_tot = use_tc ? hcap : pw_max;
     size_t need = cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) +
-                  cb_align((size_t)wmax * 12 * 8) + cb_align(pw_max * 4) + cb_align(pw_max * 8);
+                  cb_align(hcap * 12 * 8) + cb_align(n_tot * 4) + cb_align(n_tot * 8);
     if (use_tc)
-        need += cb_align((size_t)m_pad * kRtKP * 2) + cb_align((size_t)(wmax + 256) * kRtKP * 2) + cb_align((size_t)wmax * 4);
+        need += cb_align((size_t)m_pad * kRtKP * 2) + cb_align((hcap + 256) * kRtKP * 2) + cb_align(hcap * 4);
     if ((rc = cb_reserve(ctx, need))) return rc;
     RansacState* state = cb_alloc_t<RansacState>(ctx, 1);
     if (!state) return CB_ENOMEM;
@@ -639,16 +644,16 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         if (!src_xyz || !tgt_xyz) CB_FAIL(ctx, CB_EINVAL, "cb_ransac: null point arrays");
         float4* src4 = cb_alloc_t<float4>(ctx, m);
         float4* tgt4 = cb_alloc_t<float4>(ctx, m);
-        double* Tw = cb_alloc_t<double>(ctx, (size_t)wmax * 12);
-        int32_t* pc = cb_alloc_t<int32_t>(ctx, pw_max);
-        double* ps = cb_alloc_t<double>(ctx, pw_max);
+        double* Tw = cb_alloc_t<double>(ctx, hcap * 12);
+        int32_t* pc = cb_alloc_t<int32_t>(ctx, n_tot);
+        double* ps = cb_alloc_t<double>(ctx, n_tot);
         if (!src4 || !tgt4 || !Tw || !pc || !ps) return CB_ENOMEM;
         __nv_bfloat16 *Apack = nullptr, *Bpack = nullptr;
         float* band = nullptr;
         if (use_tc) {
             Bpack = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)m_pad * kRtKP);
-            Apack = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)(wmax + 256) * kRtKP);
-            band = cb_alloc_t<float>(ctx, wmax);
+            Apack = cb_alloc_t<__nv_bfloat16>(ctx, (hcap + 256) * kRtKP);
+            band = cb_alloc_t<float>(ctx, hcap);
             if (!Apack || !Bpack || !band) return CB_ENOMEM;
         }
         ransac_pack_kernel<<<cb_div_up(m, 256), 256, 0, st>>>(src_xyz, tgt_xyz, src_idx, tgt_idx, m, src4, tgt4,
@@ -661,17 +666,24 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
         int h0 = 0;
         for (int wave = 0; h0 < h_total; ++wave) {
             const int w = min(ransac_wave_size(ctx, wave), h_total - h0);
-            {
+            const size_t off = merged ? (size_t)h0 : 0;  // this wave's slice of the per-hypothesis buffers
+            double* Tw_w = Tw + off * 12;
+            int32_t* pc_w = pc + off;
+            double* ps_w = ps + off;
+            __nv_bfloat16* Apack_w = Apack ? Apack + off * kRtKP : nullptr;
+            float* band_w = band ? band + off : nullptr;
+            if (!merged || wave <= 1) {
+                const int fit_w = merged && wave == 1 ? h_total - h0 : w;
                 cb_timed_scope ts(ctx, CB_T_RANSAC_FIT, 0.0, st);
-                ransac_fit_kernel<<<cb_div_up(w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, w, ransac_n,
-                                                                     state, Tw, thr2, Apack, band,
-                                                                     use_tc ? pc : nullptr, use_tc ? ps : nullptr);
+                ransac_fit_kernel<<<cb_div_up(fit_w, 128), 128, 0, st>>>(src4, tgt4, m, minimal, seed, h0, fit_w, ransac_n,
+                                                                         state, Tw_w, thr2, Apack_w, band_w,
+                                                                         use_tc ? pc_w : nullptr, use_tc ? ps_w : nullptr);
                 CB_LAUNCH_CHECK(ctx);
             }
             int P = 1;
             if (use_tc) {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
-                if ((rc = ransac_tc_score_launch(ctx, Apack, Bpack, band, Tw, src4, tgt4, m, h0, w, thr2, state, pc, ps, st)))
+                if ((rc = ransac_tc_score_launch(ctx, Apack_w, Bpack, band_w, Tw_w, src4, tgt4, m, h0, w, thr2, state, pc_w, ps_w, st)))
                     return rc;
             } else {
                 const int groups = cb_div_up(w, 128 * 2 * NP);
@@ -680,11 +692,11 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
                 int split = cb_div_up(cb_div_up(m, P), kScoreTile) * kScoreTile;
                 P = cb_div_up(m, split);
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
-                ransac_score_kernel<NP><<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw, h0, w, thr2, state,
-                                                                     pc, ps);
+                ransac_score_kernel<NP><<<dim3(groups, P), 128, 0, st>>>(src4, tgt4, m, split, Tw_w, h0, w, thr2, state,
+                                                                     pc_w, ps_w);
                 CB_LAUNCH_CHECK(ctx);
             }
-            ransac_fold_kernel<<<1, kFoldThreads, (size_t)w * sizeof(int), st>>>(pc, ps, P, Tw, h0, w, m, ransac_n, adaptive, confidence, state,
+            ransac_fold_kernel<<<1, kFoldThreads, (size_t)w * sizeof(int), st>>>(pc_w, ps_w, P, Tw_w, h0, w, m, ransac_n, adaptive, confidence, state,
                                                  counts, sums, ctx->dev_work, src4, tgt4, thr2);
             CB_LAUNCH_CHECK(ctx);
             h0 += w;
