@@ -144,6 +144,12 @@ static int chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int
     return rc;
 }
 
+// one-direction Chamfer without the arena rewind (composite entry points, register.cu)
+int cb_chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T, double* out,
+                    cudaStream_t st) {
+    return chamfer_impl(ctx, a, na, b, nb, T, 0, 0, out, nullptr, st);
+}
+
 extern "C" int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
                           int two_dir, double* out, int32_t* nn_idx, void* stream) {
     int rc = cb_begin(ctx);

@@ -98,6 +98,14 @@ __device__ __forceinline__ int cb_draw_index(uint64_t seed, uint64_t counter, in
     return (int)(((x >> 32) * (uint64_t)(uint32_t)m) >> 32);
 }
 
-// internal entry points shared between translation units
+// internal entry points shared between translation units (none of them rewinds the arena)
+size_t cb_knn_workspace(int nq, int nr, int d, int k);
+size_t cb_ransac_workspace(const cb_ctx* ctx, int m, int h_total);
+int cb_ransac_impl(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, const int64_t* src_idx,
+                   const int64_t* tgt_idx, int m, const int32_t* minimal, uint64_t seed, int h_total, int ransac_n,
+                   double max_dist, int adaptive, double confidence, double* T, double* stats, int32_t* counts,
+                   double* sums, cudaStream_t st);
+int cb_chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T, double* out,
+                    cudaStream_t st);
 int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k,
                 int metric, int64_t* idx, float* dist, int32_t* idx32, cudaStream_t st);

@@ -283,6 +283,8 @@ static void launch_simt(const float* q, int nq, const float* r, const float* rn,
 
 const char* cb_knn_variant_name(const cb_ctx* ctx);
 
+static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k);
+
 int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k, int metric,
                 int64_t* idx, float* dist, int32_t* idx32, cudaStream_t st) {
     if (nq == 0) return CB_OK;
@@ -365,6 +367,8 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;
 }
+
+size_t cb_knn_workspace(int nq, int nr, int d, int k) { return knn_workspace(nullptr, nq, nr, d, k); }
 
 static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
     if (d > 32 || k > 12) return cb_rows_topk_workspace(nq, nr, k);

@@ -607,18 +607,25 @@ static int ransac_wave_size(const cb_ctx* ctx, int wave_index) {
     return wave_index == 0 ? kWaveFirst : ransac_wave_max(ctx);
 }
 
-extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const float* tgt_xyz, int n_tgt,
-                         const int64_t* src_idx, const int64_t* tgt_idx, int m, const int32_t* minimal,
-                         uint64_t seed, int h_total, int ransac_n, double max_dist, int adaptive,
-                         double confidence, double* T, double* stats, int32_t* counts, double* sums,
-                         void* stream) {
-    int rc = cb_begin(ctx);
-    if (rc) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
+// workspace cb_ransac_impl needs (an upper bound, both scoring variants)
+size_t cb_ransac_workspace(const cb_ctx* ctx, int m, int h_total) {
+    const size_t wmax = (size_t)ransac_wave_max(ctx);
+    const size_t hcap = (size_t)max(h_total, (int)wmax);
+    const size_t n_tot = max(hcap, size_t(5) << 18);
+    const size_t m_pad = (size_t)cb_div_up(max(m, 1), kRtTileN) * kRtTileN;
+    return cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) + cb_align(hcap * 12 * 8) +
+           cb_align(n_tot * 4) + cb_align(n_tot * 8) + cb_align(m_pad * kRtKP * 2) + cb_align((hcap + 256) * kRtKP * 2) +
+           cb_align(hcap * 4) + (1 << 16);
+}
+
+// cb_ransac without the arena rewind: callable from composite entry points (register.cu)
+int cb_ransac_impl(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, const int64_t* src_idx,
+                   const int64_t* tgt_idx, int m, const int32_t* minimal, uint64_t seed, int h_total, int ransac_n,
+                   double max_dist, int adaptive, double confidence, double* T, double* stats, int32_t* counts,
+                   double* sums, cudaStream_t st) {
+    int rc;
     if (!T || !stats || m < 0 || h_total < 0 || ransac_n > kMaxRansacN)
         CB_FAIL(ctx, CB_EINVAL, "cb_ransac: bad arguments (m=%d h=%d n=%d)", m, h_total, ransac_n);
-    (void)n_src;
-    (void)n_tgt;
     const int wmax = ransac_wave_max(ctx);
     const size_t pw_max = size_t(5) << 18;  // entries of the [P, w] partial count / sum arrays
     constexpr int NP = 2;                   // hypothesis pairs per SIMT scoring thread
@@ -705,6 +712,19 @@ extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const flo
     ransac_finish_kernel<<<1, 32, 0, st>>>(state, T, stats);
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;
+}
+
+extern "C" int cb_ransac(cb_ctx* ctx, const float* src_xyz, int n_src, const float* tgt_xyz, int n_tgt,
+                         const int64_t* src_idx, const int64_t* tgt_idx, int m, const int32_t* minimal,
+                         uint64_t seed, int h_total, int ransac_n, double max_dist, int adaptive,
+                         double confidence, double* T, double* stats, int32_t* counts, double* sums,
+                         void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    (void)n_src;
+    (void)n_tgt;
+    return cb_ransac_impl(ctx, src_xyz, tgt_xyz, src_idx, tgt_idx, m, minimal, seed, h_total, ransac_n, max_dist,
+                          adaptive, confidence, T, stats, counts, sums, (cudaStream_t)stream);
 }
 
 extern "C" int cb_set_ransac_variant(cb_ctx* ctx, int variant) {

@@ -18,7 +18,7 @@ from tqdm import tqdm
 from . import _capi
 from ._capi import ptr
 from .eval_pose import *  # noqa: F401,F403  (the reference re-exports these: utils/symmetry.py:33)
-from .eval_pose import find_kcorr, ransac_device
+from .eval_pose import CONFIDENCE, find_kcorr, ransac_device
 from .preprocess import *  # noqa: F401,F403
 
 N_NN = 50        # utils/symmetry.py:214
@@ -124,23 +124,14 @@ def _segment_perm(masks):
     return parts, off
 
 
-def _pairing_ransac(ctx, F0s, A_perm, q_off, posF_d, B_parts, xyz0_d, xyz1_d, k_nn, max_corr, seed, ransac_kw):
-    """One symmetry pairing: per-segment kNN (ragged), concatenated correspondences, RANSAC."""
-    B_perm = torch.cat(B_parts)
-    r_off = np.zeros(len(B_parts) + 1, np.int32)
-    r_off[1:] = np.cumsum([int(p.numel()) for p in B_parts])
-    F1s = posF_d[B_perm].contiguous()
-    nq = int(q_off[-1])
-    idx = ctx.empty((nq, k_nn), torch.int64)
-    ctx.call("cb_knn_ragged", ptr(F0s), ptr(F1s), F0s.shape[1], k_nn, 0,
-             q_off.ctypes.data_as(_capi.c_void_p), r_off.ctypes.data_as(_capi.c_void_p), len(B_parts),
-             ptr(idx), None, ctx.stream)
-    seg_of_q = torch.repeat_interleave(torch.arange(len(B_parts), device=ctx.device),
-                                       torch.as_tensor(np.diff(q_off), device=ctx.device))
-    base = torch.as_tensor(r_off[:-1].astype(np.int64), device=ctx.device)[seg_of_q]
-    tgt_idx = B_perm[(idx + base[:, None]).reshape(-1)]
-    src_idx = torch.repeat_interleave(A_perm, k_nn)
-    return ransac_device(xyz0_d, xyz1_d, max_corr, seed, src_idx=src_idx, tgt_idx=tgt_idx, ctx=ctx, **ransac_kw)
+def _pair_maps(K, second_sweep):
+    """pos segment matched with base segment s in every pairing of utils/symmetry.py:303-356: the K
+    cyclic rotations of the pos segments, then (pos_sym >= 2) those of [B0, B3, B2, B1]."""
+    maps = [[(s + r) % K for s in range(K)] for r in range(K)]
+    if second_sweep:
+        order = [0, 3, 2, 1]
+        maps += [[order[(s + r) % K] for s in range(K)] for r in range(K)]
+    return np.asarray(maps, dtype=np.int32)
 
 
 def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *, n_hypotheses=100000,
@@ -151,69 +142,52 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     NumPy RNG the reference draws from (``RandomState(s)`` gives the stream of ``np.random.seed(s)``);
     needed when pairs are registered concurrently (sym_pose_many).
 
+    The host only runs the two segmentations and builds the segment permutations; the vanilla
+    registration and every pairing (kNN -> RANSAC -> Chamfer each) are one cb_register_pairings call.
+
     Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success)."""
     ctx = _capi.get_context()
-    dev = ctx.device
     baseF_d = ctx.dev(baseF, torch.float32)
     posF_d = ctx.dev(posF, torch.float32)
     xyz0_d = ctx.dev(xyz0, torch.float32)
     xyz1_d = ctx.dev(xyz1, torch.float32)
-    n0 = baseF_d.shape[0]
-    rkw = dict(n_hypotheses=n_hypotheses, adaptive=adaptive)
+    n0, n1, d = baseF_d.shape[0], posF_d.shape[0], baseF_d.shape[1]
+    if n1 < k_nn:
+        raise ValueError(f"k_nn={k_nn} exceeds the {n1} target points")
 
-    def chamfer_of(T64):
-        # the reference rounds the pose to float32 before the Chamfer evaluation (:274,:280)
-        T32 = T64.to(torch.float32)
-        out = ctx.empty((1,), torch.float64)
-        Td = T32.to(torch.float64).contiguous()
-        ctx.call("cb_chamfer", ptr(xyz0_d), n0, ptr(xyz1_d), xyz1_d.shape[0], ptr(Td), 0, ptr(out), None,
-                 ctx.stream)
-        return T32, out
-
-    # vanilla: full-cloud kNN -> RANSAC -> Chamfer (:267-283)
-    idx = ctx.empty((n0, k_nn), torch.int64)
-    if posF_d.shape[0] < k_nn:
-        raise ValueError(f"k_nn={k_nn} exceeds the {posF_d.shape[0]} target points")
-    ctx.call("cb_knn", ptr(baseF_d), n0, ptr(posF_d), posF_d.shape[0], baseF_d.shape[1], k_nn, 0, ptr(idx),
-             None, None, ctx.stream)
-    src_idx = torch.repeat_interleave(torch.arange(n0, device=dev), k_nn)
-    res = ransac_device(xyz0_d, xyz1_d, max_corr, seed, src_idx=src_idx, tgt_idx=idx.reshape(-1), ctx=ctx, **rkw)
-    cands = [chamfer_of(res["T"])]
-
+    ok = True
     try:
         K = 4 if pos_sym >= 2 else 2
         base_masks = _masks_device(baseF_d, xyz0_d, K, 100, ctx, rng)
         pos_masks = _masks_device(posF_d, xyz1_d, K, 100, ctx, rng)
     except Exception as e:  # same swallow-and-fallback as utils/symmetry.py:299-301
         tqdm.write(f"symmetry failed use ransac: {e}")
-        T_r, ch_r = cands[0]
-        T_r, ch_r = T_r.cpu(), float(ch_r.item())
-        return T_r, ch_r, T_r, ch_r, False
+        ok = False
 
-    A_parts, q_off = _segment_perm(base_masks)
-    A_perm = torch.cat(A_parts)
-    F0s = baseF_d[A_perm].contiguous()
-    B_parts = [torch.nonzero(m, as_tuple=False).reshape(-1) for m in pos_masks]
-
-    def sweep(parts):
-        for _ in range(len(parts)):
-            r = _pairing_ransac(ctx, F0s, A_perm, q_off, posF_d, parts, xyz0_d, xyz1_d, k_nn, max_corr, seed, rkw)
-            cands.append(chamfer_of(r["T"]))
-            parts.append(parts.pop(0))
-        return parts
-
-    B_parts = sweep(B_parts)
-    if pos_sym >= 2:
-        B_parts = sweep([B_parts[0], B_parts[3], B_parts[2], B_parts[1]])
-
-    chamf = torch.cat([c for _, c in cands]).cpu().numpy()  # the one synchronisation of the sweep
+    if ok:
+        A_parts, q_off = _segment_perm(base_masks)
+        B_parts, r_off = _segment_perm(pos_masks)
+        A_perm, B_perm = torch.cat(A_parts), torch.cat(B_parts)
+        maps = _pair_maps(K, pos_sym >= 2)
+        P = len(maps)
+    else:
+        A_perm = B_perm = None
+        q_off = r_off = maps = np.zeros(1, np.int32)
+        K, P = 0, 0
+    T_all = ctx.empty((1 + P, 4, 4), torch.float64)
+    chamf_d = ctx.empty((1 + P,), torch.float64)
+    ctx.call("cb_register_pairings", ptr(baseF_d), ptr(xyz0_d), n0, ptr(posF_d), ptr(xyz1_d), n1, d, int(k_nn),
+             ptr(A_perm), q_off.ctypes.data_as(_capi.c_void_p), ptr(B_perm), r_off.ctypes.data_as(_capi.c_void_p), K,
+             maps.ctypes.data_as(_capi.c_void_p), P, float(max_corr), int(seed) & 0xFFFFFFFFFFFFFFFF,
+             int(n_hypotheses), int(bool(adaptive)), CONFIDENCE, ptr(T_all), ptr(chamf_d), None, ctx.stream)
+    out = torch.cat([T_all.reshape(-1), chamf_d]).cpu().numpy()  # the one synchronisation of the sweep
+    Ts = torch.from_numpy(out[:16 * (1 + P)].reshape(1 + P, 4, 4).astype(np.float32))
+    chamf = out[16 * (1 + P):]
     best = 0
-    for i in range(1, len(cands)):
+    for i in range(1, 1 + P):
         if chamf[best] > chamf[i]:  # strictly lower Chamfer wins (:321,:353)
             best = i
-    T_ransac = cands[0][0].cpu()
-    T_best = cands[best][0].cpu()
-    return T_best, float(chamf[best]), T_ransac, float(chamf[0]), True
+    return Ts[best], float(chamf[best]), Ts[0], float(chamf[0]), ok
 
 
 # ---------------------------------------------------------------------------------------------

@@ -202,6 +202,27 @@ int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx,
 int cb_assign_labels(cb_ctx* ctx, const float* xyz, int n, const float* centers, int K,
                      int32_t* labels, int32_t* counts, void* stream);
 
+/* ---- sym_pose body in one call (utils/symmetry.py:262-358) -----------------------------------
+ * The vanilla registration (:267-283: feature kNN over the whole clouds -> correspondence RANSAC
+ * with ransac_n = 10 and the seeded counter-based draws -> one-direction Chamfer of the
+ * float32-rounded pose) followed by n_pairings symmetry pairings (:303-356, split_corr per
+ * pairing: per-segment kNN, concatenated correspondences -> RANSAC -> Chamfer), all enqueued on
+ * `stream` without host synchronisation.
+ * base_f [n0,d], base_xyz [n0,3], pos_f [n1,d], pos_xyz [n1,3] float32 (device).
+ * a_perm [n0] / b_perm [n1] int64 (device): point indices sorted by segment (ascending index
+ * inside a segment); h_q_off / h_r_off [n_seg+1] int32 (HOST): segment offsets into them.
+ * h_pair_map [n_pairings, n_seg] int32 (HOST): pairing p matches base segment s with pos segment
+ * h_pair_map[p][s].  n_pairings = 0 runs the vanilla registration only (perms may be NULL).
+ * Outputs (device): T_out [(1+n_pairings),16] float64 holding float32-rounded poses (vanilla
+ * first), chamfer_out [(1+n_pairings)] float64, stats_out (may be NULL) [(1+n_pairings),4] as
+ * cb_ransac's stats. */
+int cb_register_pairings(cb_ctx* ctx, const float* base_f, const float* base_xyz, int n0,
+                         const float* pos_f, const float* pos_xyz, int n1, int d, int k_nn,
+                         const int64_t* a_perm, const int32_t* h_q_off, const int64_t* b_perm,
+                         const int32_t* h_r_off, int n_seg, const int32_t* h_pair_map, int n_pairings,
+                         double max_dist, uint64_t seed, int h_total, int adaptive, double confidence,
+                         double* T_out, double* chamfer_out, double* stats_out, void* stream);
+
 /* ---- K5: IRLS pose (utils/_transform_estimation.py:110-137) ------------------------------
  * est_quad_linear_robust: iters (reference: 20) iterations of the linearised weighted solve.
  * p0,p1 [n,3] float32, w [n] float32 (NULL = ones); T [16] float32 (device). */

@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""GPU occupancy of the threaded bench step: kineto trace of a few steps, then the union of the
+kernel intervals (busy time), the summed kernel time (overlap) and the per-kernel totals.
+Diagnostic only."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+
+def main():
+    steps = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+    from corsair_b200 import get_context, retrieval, symmetry
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    get_context(0)
+    lib, cads, queries = bench.build_workload(0)
+    lib_d = torch.from_numpy(lib).to(dev)
+    cads_d = [dict(F=torch.from_numpy(c["F"]).to(dev), xyz=torch.from_numpy(c["xyz"]).to(dev), sym=c["sym"]) for c in cads]
+    qs = [dict(desc=torch.from_numpy(q["desc"]).to(dev), F=torch.from_numpy(q["F"]).to(dev),
+               xyz=torch.from_numpy(q["xyz"]).to(dev)) for q in queries]
+    for i in range(3):
+        bench.gpu_step(retrieval, symmetry, lib_d, cads_d, qs[i])
+    torch.cuda.synchronize()
+    from torch.profiler import ProfilerActivity, profile
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        t0 = time.perf_counter()
+        for i in range(steps):
+            bench.gpu_step(retrieval, symmetry, lib_d, cads_d, qs[3 + i])
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / steps
+    path = os.path.join(ROOT, "gpurun_out", "trace_threads.json")
+    prof.export_chrome_trace(path)
+    ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
+    iv = sorted((e["ts"], e["ts"] + e["dur"]) for e in ev)
+    busy, cur_s, cur_e = 0.0, None, None
+    for s, e in iv:
+        if cur_e is None or s > cur_e:
+            if cur_e is not None:
+                busy += cur_e - cur_s
+            cur_s, cur_e = s, e
+        else:
+            cur_e = max(cur_e, e)
+    busy += cur_e - cur_s
+    total = sum(e["dur"] for e in ev)
+    span = iv[-1][1] - iv[0][0]
+    print(f"wall/step {wall*1e3:.2f} ms; per step: span {span/steps/1e3:.2f} ms, busy (union) {busy/steps/1e3:.2f} ms, "
+          f"summed kernel time {total/steps/1e3:.2f} ms")
+    agg = {}
+    for e in ev:
+        n = e["name"][:60]
+        a = agg.setdefault(n, [0, 0.0])
+        a[0] += 1
+        a[1] += e["dur"]
+    for n, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]:
+        print(f"  {d/steps/1e3:8.3f} ms/step  {c/steps:7.1f} launches/step  avg {d/c:7.1f} us  {n}")
+    os.remove(path)
+
+
+if __name__ == "__main__":
+    main()
