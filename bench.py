@@ -152,7 +152,7 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
-WORKERS = int(os.environ.get("CB_BENCH_WORKERS", "4"))  # host threads (each with its own cb_ctx + CUDA stream) registering a step's pairs
+WORKERS = int(os.environ.get("CB_BENCH_WORKERS", "5"))  # host threads (each with its own cb_ctx + CUDA stream) registering a step's pairs
 
 
 def gpu_step(retrieval, symmetry, lib_in, cads_in, q, workers=WORKERS):

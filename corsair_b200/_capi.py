@@ -61,6 +61,8 @@ SIGNATURES = {
                                 c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "cb_assign_labels": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
                                  c_void_p]),
+    "cb_symmetry_segments": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_double, c_void_p,
+                                     c_void_p, c_void_p, c_void_p]),
     "cb_register_pairings": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_u64,
                                      c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -283,6 +283,115 @@ __global__ void assign_labels_kernel(const float* __restrict__ xyz, int n, const
     if (counts && threadIdx.x < K && hist[threadIdx.x]) atomicAdd(&counts[threadIdx.x], hist[threadIdx.x]);
 }
 
+// Model selection + labels + segment permutation in one block (no host round trip):
+//   thread 0 replays the sequential acceptance rule of utils/symmetry.py:233-235 over the S rows of
+//   statistics and, for K = 4, the centre ranking of :239-244 (float32 norms like NumPy's);
+//   every thread then labels its contiguous slice of points (KMeans.predict, :246) and the block
+//   writes, per segment in the reference's order, the ascending indices of its points.
+// out_off [K+2]: segment offsets [K+1], then the winning sample (-1: no model accepted).
+__global__ void __launch_bounds__(1024)
+segments_kernel(const float* __restrict__ xyz, int n, const float* __restrict__ centers,
+                const double* __restrict__ stats, int S, int K, double min_center,
+                int64_t* __restrict__ perm, int32_t* __restrict__ labels_out, int32_t* __restrict__ out_off) {
+    __shared__ float c[kKmMaxK][3];
+    __shared__ int seg_of_label[kKmMaxK];
+    __shared__ int s_win;
+    __shared__ int cnt[4][1024];
+    __shared__ int seg_base[5];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        double curr_var = 100.0;
+        int win = -1;
+        for (int i = 0; i < S; ++i) {
+            const double dmin = stats[4 * i], emax = stats[4 * i + 1], sd = stats[4 * i + 2];
+            if (dmin > min_center && min_center > emax && curr_var > sd) { curr_var = sd; win = i; }
+        }
+        s_win = win;
+        if (win >= 0) {
+            for (int k = 0; k < K; ++k)
+                for (int a = 0; a < 3; ++a) c[k][a] = centers[((size_t)win * K + k) * 3 + a];
+            int order[4] = {0, 1, 2, 3};
+            if (K == 4) {
+                float d[3];
+                for (int j = 1; j < 4; ++j) {
+                    const float dx = c[j][0] - c[0][0], dy = c[j][1] - c[0][1], dz = c[j][2] - c[0][2];
+                    d[j - 1] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+                }
+                int r[3] = {0, 1, 2};  // stable argsort of three values
+                for (int a = 1; a < 3; ++a)
+                    for (int b = a; b > 0 && d[r[b]] < d[r[b - 1]]; --b) { int t = r[b]; r[b] = r[b - 1]; r[b - 1] = t; }
+                order[1] = r[0] + 1; order[2] = r[2] + 1; order[3] = r[1] + 1;
+            }
+            for (int s = 0; s < K; ++s) seg_of_label[order[s]] = s;
+        }
+    }
+    __syncthreads();
+    if (s_win < 0) {
+        if (tid <= K) out_off[tid] = 0;
+        if (tid == 0) out_off[K + 1] = -1;
+        return;
+    }
+    const int per = (n + 1023) / 1024;
+    const int i0 = min(n, tid * per), i1 = min(n, i0 + per);
+    int my[4] = {0, 0, 0, 0};
+    for (int i = i0; i < i1; ++i) {
+        const float p[3] = {xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2]};
+        const int l = km_nearest(p, c, K);
+        if (labels_out) labels_out[i] = l;
+        const int s = seg_of_label[l];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) my[q] += (s == q);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) cnt[q][tid] = my[q];
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31;
+    if (warp < 4) {  // exclusive scan of segment `warp` over the 1024 slices
+        int v[32], tot = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { v[j] = cnt[warp][lane * 32 + j]; tot += v[j]; }
+        int inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+        int run = inc - tot;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { cnt[warp][lane * 32 + j] = run; run += v[j]; }
+        if (lane == 31) seg_base[warp + 1] = inc;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        seg_base[0] = 0;
+        for (int s = 1; s <= 4; ++s) seg_base[s] += seg_base[s - 1];
+        for (int s = 0; s <= K; ++s) out_off[s] = seg_base[s];
+        out_off[K + 1] = s_win;
+    }
+    __syncthreads();
+    int pos[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pos[q] = seg_base[q] + cnt[q][tid];
+    for (int i = i0; i < i1; ++i) {
+        const float p[3] = {xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2]};
+        const int s = seg_of_label[km_nearest(p, c, K)];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (s == q) perm[pos[q]++] = i;
+    }
+}
+
+extern "C" int cb_symmetry_segments(cb_ctx* ctx, const float* xyz, int n, const float* centers, const double* stats,
+                                    int n_samples, int K, double min_center, int64_t* perm, int32_t* labels,
+                                    int32_t* seg_off, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    if (!xyz || !centers || !stats || !perm || !seg_off || n <= 0 || n_samples < 0)
+        CB_FAIL(ctx, CB_EINVAL, "cb_symmetry_segments: bad arguments");
+    if (K != 2 && K != 4) CB_FAIL(ctx, CB_EUNSUPPORTED, "cb_symmetry_segments: K must be 2 or 4 (got %d)", K);
+    segments_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(xyz, n, centers, stats, n_samples, K, min_center, perm, labels,
+                                                          seg_off);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
 extern "C" int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx, int n_samples,
                                int n_nn, int K, const int32_t* rng_first, const double* rng_unif, int n_init,
                                int n_trials, float* centers, double* stats, void* stream) {

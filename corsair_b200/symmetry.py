@@ -64,8 +64,10 @@ def cut_model_device(feat_d, xyz_d, K, random_points, ctx):
     samp = ctx.dev(np.asarray(random_points, dtype=np.int32), torch.int32)
     nn_idx = ctx.empty((S, n_nn), torch.int32)
     ctx.call("cb_feature_rows_topk", ptr(feat_d), n, d, ptr(samp), S, n_nn, ptr(nn_idx), ctx.stream)
-    first_d = ctx.dev(first, torch.int32)
-    unif_d = ctx.dev(unif, torch.float64)
+    cache = ctx.__dict__.setdefault("_km_draws", {})  # data-independent: uploaded once per context
+    if (n_nn, K) not in cache:
+        cache[(n_nn, K)] = (ctx.dev(first, torch.int32), ctx.dev(unif, torch.float64))
+    first_d, unif_d = cache[(n_nn, K)]
     centers = ctx.empty((S, K, 3), torch.float32)
     stats = ctx.empty((S, 4), torch.float64)
     ctx.call("cb_kmeans_batch", ptr(xyz_d), n, ptr(nn_idx), S, n_nn, K, ptr(first_d), ptr(unif_d), N_INIT,
@@ -108,20 +110,28 @@ def _masks_device(feat_d, xyz_d, K, max_sample, ctx, rng=None):
     return [labels == int(o) for o in order]
 
 
+def _segments_device(feat_d, xyz_d, K, max_sample, ctx, rng=None):
+    """symmetric_cut4 without a host round trip: (perm [n] int64, seg_off [K+2] int32) on the device
+    — the concatenated ascending point indices of the K masks, their offsets and the accepted
+    sample (-1: none).  Nothing is synchronised here."""
+    if K not in (2, 4):
+        raise ValueError("not defined")
+    n = xyz_d.shape[0]
+    random_points = (rng or np.random).choice(n, max_sample, replace=False)
+    centers, stats, _ = cut_model_device(feat_d, xyz_d, K, random_points, ctx)
+    perm = ctx.empty((n,), torch.int64)
+    seg_off = ctx.empty((K + 2,), torch.int32)
+    ctx.call("cb_symmetry_segments", ptr(xyz_d), n, ptr(centers), ptr(stats), len(random_points), K, MIN_CENTER,
+             ptr(perm), None, ptr(seg_off), ctx.stream)
+    return perm, seg_off
+
+
 def symmetric_cut4(feat, raw_pc, K, max_sample=100):
     """utils/symmetry.py:182-259 -> list of K boolean NumPy masks over the N points."""
     ctx = _capi.get_context()
     feat_d = ctx.dev(feat, torch.float32)
     xyz_d = ctx.dev(raw_pc, torch.float32)
     return [m.cpu().numpy() for m in _masks_device(feat_d, xyz_d, K, max_sample, ctx)]
-
-
-def _segment_perm(masks):
-    """Concatenated ascending point indices of each segment and the segment offsets."""
-    parts = [torch.nonzero(m, as_tuple=False).reshape(-1) for m in masks]
-    off = np.zeros(len(parts) + 1, np.int32)
-    off[1:] = np.cumsum([int(p.numel()) for p in parts])
-    return parts, off
 
 
 def _pair_maps(K, second_sweep):
@@ -155,22 +165,31 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     if n1 < k_nn:
         raise ValueError(f"k_nn={k_nn} exceeds the {n1} target points")
 
-    ok = True
-    try:
-        K = 4 if pos_sym >= 2 else 2
-        base_masks = _masks_device(baseF_d, xyz0_d, K, 100, ctx, rng)
-        pos_masks = _masks_device(posF_d, xyz1_d, K, 100, ctx, rng)
-    except Exception as e:  # same swallow-and-fallback as utils/symmetry.py:299-301
-        tqdm.write(f"symmetry failed use ransac: {e}")
-        ok = False
-
+    # both segmentations are enqueued, then ONE read brings back the segment offsets.  The reference
+    # (utils/symmetry.py:289-301) segments pos only when base succeeded: if base fails, the NumPy
+    # stream is rewound so that exactly the draws the reference makes are consumed.
+    K = 4 if pos_sym >= 2 else 2
+    src = rng or np.random
+    why = None
+    try:  # same swallow-and-fallback as utils/symmetry.py:292-301
+        A_perm, offA = _segments_device(baseF_d, xyz0_d, K, 100, ctx, rng)
+        rewind = src.get_state()
+        B_perm, offB = _segments_device(posF_d, xyz1_d, K, 100, ctx, rng)
+        off = torch.stack([offA, offB]).cpu().numpy()
+        if off[0, K + 1] < 0:
+            src.set_state(rewind)
+        if off[0, K + 1] < 0 or off[1, K + 1] < 0:
+            # the reference dereferences curr_model = None here (utils/symmetry.py:237)
+            why = "'NoneType' object has no attribute 'cluster_centers_'"
+    except Exception as e:
+        why = str(e)
+    ok = why is None
     if ok:
-        A_parts, q_off = _segment_perm(base_masks)
-        B_parts, r_off = _segment_perm(pos_masks)
-        A_perm, B_perm = torch.cat(A_parts), torch.cat(B_parts)
+        q_off, r_off = np.ascontiguousarray(off[0, :K + 1]), np.ascontiguousarray(off[1, :K + 1])
         maps = _pair_maps(K, pos_sym >= 2)
         P = len(maps)
     else:
+        tqdm.write(f"symmetry failed use ransac: {why}")
         A_perm = B_perm = None
         q_off = r_off = maps = np.zeros(1, np.int32)
         K, P = 0, 0

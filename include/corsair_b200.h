@@ -202,6 +202,17 @@ int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx,
 int cb_assign_labels(cb_ctx* ctx, const float* xyz, int n, const float* centers, int K,
                      int32_t* labels, int32_t* counts, void* stream);
 
+/* Model selection (utils/symmetry.py:233-235), KMeans.predict of the winner over all n points
+ * (:246), the K = 4 centre ranking (:239-244) and the resulting segment permutation, without a host round trip.
+ * centers [n_samples,K,3] f32 and stats [n_samples,4] f64 as written by cb_kmeans_batch.
+ * perm [n] int64: ascending point indices of segment 0, then segment 1, ... in the order of the masks
+ * symmetric_cut4 returns (:248-256); labels [n] int32 (may be NULL); seg_off [K+2] int32 (DEVICE):
+ * K+1 segment offsets, then the accepted sample (-1: none — the reference raises there, :237).
+ * K must be 2 or 4 (:257-258). */
+int cb_symmetry_segments(cb_ctx* ctx, const float* xyz, int n, const float* centers, const double* stats,
+                         int n_samples, int K, double min_center, int64_t* perm, int32_t* labels,
+                         int32_t* seg_off, void* stream);
+
 /* ---- sym_pose body in one call (utils/symmetry.py:262-358) -----------------------------------
  * The vanilla registration (:267-283: feature kNN over the whole clouds -> correspondence RANSAC
  * with ransac_n = 10 and the seeded counter-based draws -> one-direction Chamfer of the

@@ -51,6 +51,58 @@ def test_symmetric_cut4_masks(ctx, category, K):
     assert same_winner >= 2, f"device segmentation agrees with the reference on {same_winner}/3 clouds"
 
 
+@pytest.mark.parametrize("category,K", [("chair", 2), ("table", 4), ("chair", 4), ("table", 2)])
+def test_segments_device_equals_masks(ctx, category, K):
+    """cb_symmetry_segments (selection rule + labels + centre ranking + permutation on the device)
+    against the host-side selection of symmetric_cut4 on the same draws: bit-exact."""
+    from corsair_b200 import symmetry
+    for seed in range(3):
+        p = synth.make_pair(seed, 32, category)
+        feat_d, xyz_d = ctx.dev(p["posF"], torch.float32), ctx.dev(p["xyz1"], torch.float32)
+        try:
+            masks = symmetry._masks_device(feat_d, xyz_d, K, 100, ctx, np.random.RandomState(5))
+        except AttributeError:
+            masks = None
+        perm, off = symmetry._segments_device(feat_d, xyz_d, K, 100, ctx, np.random.RandomState(5))
+        perm, off = perm.cpu().numpy(), off.cpu().numpy()
+        if masks is None:
+            assert off[K + 1] == -1 and not off[:K + 1].any()
+            continue
+        assert off[K + 1] >= 0 and off[0] == 0 and off[K] == len(p["xyz1"])
+        want = [np.nonzero(m.cpu().numpy())[0] for m in masks]
+        assert np.array_equal(np.diff(off[:K + 1]), [len(w) for w in want])
+        assert np.array_equal(perm, np.concatenate(want))
+
+
+def test_segments_device_no_model(ctx, rng):
+    """No sample passes the acceptance rule -> winner -1, zero offsets (the reference raises, :237)."""
+    from corsair_b200 import symmetry
+    n, K, S = 3000, 2, 7
+    xyz = ctx.dev(rng.standard_normal((n, 3)).astype(np.float32), torch.float32)
+    centers = ctx.dev(rng.standard_normal((S, K, 3)).astype(np.float32), torch.float32)
+    stats = np.tile(np.array([0.1, 0.05, 0.2, 0.0]), (S, 1))  # min centre distance below 0.15
+    stats[3, 1] = np.nan
+    perm, off = ctx.empty((n,), torch.int64), ctx.empty((K + 2,), torch.int32)
+    from corsair_b200._capi import ptr
+    ctx.call("cb_symmetry_segments", ptr(xyz), n, ptr(centers), ptr(ctx.dev(stats, torch.float64)), S, K, 0.15, ptr(perm),
+             None, ptr(off), ctx.stream)
+    assert off.cpu().tolist() == [0, 0, 0, -1]
+    # one acceptable row, a better (lower ratio std) one later, and a NaN error row in between
+    stats[1] = [0.3, 0.1, 0.4, 0.0]
+    stats[3] = [0.3, np.nan, 0.0, 0.0]
+    stats[5] = [0.3, 0.1, 0.2, 0.0]
+    stats[6] = [0.3, 0.1, 0.2, 0.0]  # equal std: the earlier row stays
+    labels = ctx.empty((n,), torch.int32)
+    ctx.call("cb_symmetry_segments", ptr(xyz), n, ptr(centers), ptr(ctx.dev(stats, torch.float64)), S, K, 0.15, ptr(perm),
+             ptr(labels), ptr(off), ctx.stream)
+    off, perm, labels = off.cpu().numpy(), perm.cpu().numpy(), labels.cpu().numpy()
+    assert off[K + 1] == 5 == symmetry.select_cut(stats)
+    ref = ctx.empty((n,), torch.int32)
+    ctx.call("cb_assign_labels", ptr(xyz), n, ptr(centers[5].contiguous()), K, ptr(ref), None, ctx.stream)
+    assert np.array_equal(labels, ref.cpu().numpy())
+    assert np.array_equal(perm, np.concatenate([np.nonzero(labels == 0)[0], np.nonzero(labels == 1)[0]]))
+
+
 def test_kmeans_batch_stats_vs_sklearn(ctx):
     """Per-sample statistics (min centre distance, max error, ratio std) against sklearn on the
     same 50-point neighbourhoods."""
