@@ -164,7 +164,7 @@ def gpu_step(retrieval, symmetry, lib_in, cads_in, q, workers=WORKERS):
     for c in idx[0]:
         cad = cads_in[int(c) % CAD_POOL]
         jobs.append(((q["F"], q["xyz"], cad["F"], cad["xyz"], cad["sym"]),
-                     dict(k_nn=K_NN, max_corr=MAX_CORR, seed=SEED, rng=np.random.RandomState(SEED))))
+                     dict(k_nn=K_NN, max_corr=MAX_CORR, seed=SEED, rng=SEED)))
     return symmetry.sym_pose_many(jobs, workers=workers)
 
 

@@ -45,6 +45,11 @@ extern "C" int cb_destroy(cb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->arena) cudaFree(ctx->arena);
     if (ctx->dev_work) cudaFree(ctx->dev_work);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto e : ctx->sub_event) cudaEventDestroy(e);
+    for (auto s : ctx->sub_stream) cudaStreamDestroy(s);
+    for (auto c : ctx->sub) cb_destroy(c);
+    if (ctx->fork_event) cudaEventDestroy(ctx->fork_event);
     for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;

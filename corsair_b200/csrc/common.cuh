@@ -31,6 +31,13 @@ struct cb_ctx {
     double cls_work[CB_TIMING_CLASSES] = {0};
     int64_t cls_launches[CB_TIMING_CLASSES] = {0};
     double* dev_work = nullptr;  // [CB_TIMING_CLASSES] device-side work counters (RANSAC waves that ran)
+    // cb_sym_pose: pinned staging for its small host<->device traffic, and the sub-contexts (own
+    // arena + stream each) its independent registrations run on
+    char* pinned = nullptr;
+    std::vector<cb_ctx*> sub;
+    std::vector<cudaStream_t> sub_stream;
+    std::vector<cudaEvent_t> sub_event;
+    cudaEvent_t fork_event = nullptr;
 };
 
 // Bracket one tracked launch with events when timing is on.
@@ -109,3 +116,7 @@ int cb_chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int nb,
                     cudaStream_t st);
 int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int k,
                 int metric, int64_t* idx, float* dist, int32_t* idx32, cudaStream_t st);
+size_t cb_segment_workspace(int n, int n_samples, int n_nn, int K);
+int cb_segment_impl(cb_ctx* ctx, const float* feat, const float* xyz, int n, int d, int K, const int32_t* d_samples,
+                    int n_samples, int n_nn, const int32_t* d_first, const double* d_unif, int n_init, int n_trials,
+                    double min_center, int64_t* perm, int32_t* seg_off, cudaStream_t st);

@@ -10,6 +10,7 @@
 // reproducible, so agreement is exact except where a decision sits on a float32 rounding tie;
 // tests report the mask-equality rate against the reference.
 #include "common.cuh"
+#include "knn_internal.cuh"
 
 #include <math.h>
 
@@ -392,6 +393,23 @@ extern "C" int cb_symmetry_segments(cb_ctx* ctx, const float* xyz, int n, const 
     return CB_OK;
 }
 
+static int kmeans_launch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx, int n_samples, int n_nn, int K,
+                         const int32_t* rng_first, const double* rng_unif, int n_init, int n_trials, float* centers,
+                         double* stats, cudaStream_t st) {
+    if (n_nn > kKmMaxPts || K > kKmMaxK || K > n_nn || n_init < 1 || n_init > kKmMaxInit || n_trials < 1 ||
+        n_trials > 4)
+        CB_FAIL(ctx, CB_EUNSUPPORTED, "cb_kmeans_batch: n_nn<=64, K<=8, n_init<=16, n_trials<=4 (got %d %d %d %d)",
+                n_nn, K, n_init, n_trials);
+    size_t smem = sizeof(KmWarp) * n_init;
+    cudaError_t e = cudaFuncSetAttribute(kmeans_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "smem opt-in failed: %s", cudaGetErrorString(e));
+    cb_timed_scope ts(ctx, CB_T_KMEANS, 0.0, st);
+    kmeans_batch_kernel<<<n_samples, 32 * n_init, smem, st>>>(xyz, n, nn_idx, n_nn, K, rng_first, rng_unif, n_init,
+                                                             n_trials, centers, stats);
+    CB_LAUNCH_CHECK(ctx);
+    return CB_OK;
+}
+
 extern "C" int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32_t* nn_idx, int n_samples,
                                int n_nn, int K, const int32_t* rng_first, const double* rng_unif, int n_init,
                                int n_trials, float* centers, double* stats, void* stream) {
@@ -400,16 +418,33 @@ extern "C" int cb_kmeans_batch(cb_ctx* ctx, const float* xyz, int n, const int32
     if (n_samples == 0) return CB_OK;
     if (!xyz || !nn_idx || !rng_first || !rng_unif || !centers || !stats || n <= 0 || n_nn < 1 || K < 1)
         CB_FAIL(ctx, CB_EINVAL, "cb_kmeans_batch: bad arguments");
-    if (n_nn > kKmMaxPts || K > kKmMaxK || K > n_nn || n_init < 1 || n_init > kKmMaxInit || n_trials < 1 ||
-        n_trials > 4)
-        CB_FAIL(ctx, CB_EUNSUPPORTED, "cb_kmeans_batch: n_nn<=64, K<=8, n_init<=16, n_trials<=4 (got %d %d %d %d)",
-                n_nn, K, n_init, n_trials);
-    size_t smem = sizeof(KmWarp) * n_init;
-    cudaError_t e = cudaFuncSetAttribute(kmeans_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "smem opt-in failed: %s", cudaGetErrorString(e));
-    cb_timed_scope ts(ctx, CB_T_KMEANS, 0.0, (cudaStream_t)stream);
-    kmeans_batch_kernel<<<n_samples, 32 * n_init, smem, (cudaStream_t)stream>>>(
-        xyz, n, nn_idx, n_nn, K, rng_first, rng_unif, n_init, n_trials, centers, stats);
+    return kmeans_launch(ctx, xyz, n, nn_idx, n_samples, n_nn, K, rng_first, rng_unif, n_init, n_trials, centers, stats,
+                         (cudaStream_t)stream);
+}
+
+// symmetric_cut4 end to end on one stream (internal; allocates from the arena without rewinding it):
+// feature-space neighbourhoods of the sampled rows -> batched k-means -> selection + permutation
+size_t cb_segment_workspace(int n, int n_samples, int n_nn, int K) {
+    return cb_rows_topk_workspace(n_samples, n, n_nn) + cb_align((size_t)n_samples * n_nn * 4) +
+           cb_align((size_t)n_samples * K * 12) + cb_align((size_t)n_samples * 32) + 4096;
+}
+
+int cb_segment_impl(cb_ctx* ctx, const float* feat, const float* xyz, int n, int d, int K, const int32_t* d_samples,
+                    int n_samples, int n_nn, const int32_t* d_first, const double* d_unif, int n_init, int n_trials,
+                    double min_center, int64_t* perm, int32_t* seg_off, cudaStream_t st) {
+    if (K != 2 && K != 4) CB_FAIL(ctx, CB_EUNSUPPORTED, "symmetry segmentation: K must be 2 or 4 (got %d)", K);
+    if (n_nn < 1 || n_nn > n || n_samples < 1) CB_FAIL(ctx, CB_EINVAL, "symmetry segmentation: bad sample sizes");
+    int32_t* nn_idx = cb_alloc_t<int32_t>(ctx, (size_t)n_samples * n_nn);
+    float* centers = cb_alloc_t<float>(ctx, (size_t)n_samples * K * 3);
+    double* stats = cb_alloc_t<double>(ctx, (size_t)n_samples * 4);
+    if (!nn_idx || !centers || !stats) return CB_ENOMEM;
+    int rc = cb_rows_topk(ctx, feat, n_samples, feat, n, d, n_nn, 0, 0, 0, 1, nullptr, nn_idx, nullptr, nullptr, 0,
+                          d_samples, st);
+    if (rc) return rc;
+    if ((rc = kmeans_launch(ctx, xyz, n, nn_idx, n_samples, n_nn, K, d_first, d_unif, n_init, n_trials, centers, stats,
+                            st)))
+        return rc;
+    segments_kernel<<<1, 1024, 0, st>>>(xyz, n, centers, stats, n_samples, K, min_center, perm, nullptr, seg_off);
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;
 }

@@ -148,12 +148,14 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
              adaptive=True, rng=None):
     """utils/symmetry.py:262-358: pose with and without the symmetry-aided pairing search.
 
-    ``rng``: a ``np.random.RandomState`` for the segmentation's seed points instead of the global
-    NumPy RNG the reference draws from (``RandomState(s)`` gives the stream of ``np.random.seed(s)``);
-    needed when pairs are registered concurrently (sym_pose_many).
+    ``rng``: where the segmentation's seed points come from instead of the global NumPy RNG the
+    reference draws from — a ``np.random.RandomState``, or an int ``s``: the points
+    ``np.random.seed(s)`` followed by the two ``choice`` calls would give, replayed inside the C call
+    (no interpreter time); one of the two is needed when pairs are registered concurrently
+    (sym_pose_many).
 
-    The host only runs the two segmentations and builds the segment permutations; the vanilla
-    registration and every pairing (kNN -> RANSAC -> Chamfer each) are one cb_register_pairings call.
+    Everything after the seed-row draws — both segmentations, the vanilla registration and every
+    pairing (kNN -> RANSAC -> Chamfer each) — is one cb_sym_pose call.
 
     Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success)."""
     ctx = _capi.get_context()
@@ -165,48 +167,47 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     if n1 < k_nn:
         raise ValueError(f"k_nn={k_nn} exceeds the {n1} target points")
 
-    # both segmentations are enqueued, then ONE read brings back the segment offsets.  The reference
-    # (utils/symmetry.py:289-301) segments pos only when base succeeded: if base fails, the NumPy
-    # stream is rewound so that exactly the draws the reference makes are consumed.
+    # host side of the pair: the two seed-row draws (global NumPy RNG like utils/symmetry.py:193
+    # unless the caller hands in a RandomState), then ONE C call that releases the GIL until the
+    # poses are back on the host.  The reference segments pos only when base succeeded (:292-301):
+    # if base accepts no model, the stream is rewound to where the reference would have left it.
     K = 4 if pos_sym >= 2 else 2
-    src = rng or np.random
-    why = None
-    try:  # same swallow-and-fallback as utils/symmetry.py:292-301
-        A_perm, offA = _segments_device(baseF_d, xyz0_d, K, 100, ctx, rng)
-        rewind = src.get_state()
-        B_perm, offB = _segments_device(posF_d, xyz1_d, K, 100, ctx, rng)
-        off = torch.stack([offA, offB]).cpu().numpy()
-        if off[0, K + 1] < 0:
-            src.set_state(rewind)
-        if off[0, K + 1] < 0 or off[1, K + 1] < 0:
-            # the reference dereferences curr_model = None here (utils/symmetry.py:237)
-            why = "'NoneType' object has no attribute 'cluster_centers_'"
-    except Exception as e:
-        why = str(e)
-    ok = why is None
-    if ok:
-        q_off, r_off = np.ascontiguousarray(off[0, :K + 1]), np.ascontiguousarray(off[1, :K + 1])
-        maps = _pair_maps(K, pos_sym >= 2)
-        P = len(maps)
+    why, rewind, n_s, np_seed = None, None, 100, -1
+    s_base = s_pos = None
+    if isinstance(rng, (int, np.integer)):
+        np_seed = int(rng)  # drawn inside the call, as after np.random.seed(rng)
+        if not 0 <= np_seed < 2 ** 32:
+            raise ValueError("Seed must be between 0 and 2**32 - 1")
+        if min(n0, n1) < n_s:
+            why = "Cannot take a larger sample than population when 'replace=False'"
     else:
+        src = rng or np.random
+        try:  # same swallow-and-fallback as utils/symmetry.py:292-301
+            s_base = src.choice(n0, n_s, replace=False).astype(np.int32)
+            rewind = src.get_state()
+            s_pos = src.choice(n1, n_s, replace=False).astype(np.int32)
+        except Exception as e:
+            why, n_s = str(e), 0
+            s_base = s_pos = None
+    n_nn = min(N_NN, n0, n1)
+    first, unif, n_trials = _kmeanspp_draws(n_nn, K)
+    out = np.empty(40, np.float64)
+    vp = _capi.c_void_p
+    ctx.call("cb_sym_pose", ptr(baseF_d), ptr(xyz0_d), n0, ptr(posF_d), ptr(xyz1_d), n1, d, int(pos_sym), int(k_nn),
+             s_base.ctypes.data_as(vp) if s_base is not None else None,
+             s_pos.ctypes.data_as(vp) if s_pos is not None else None, n_s, np_seed, n_nn, first.ctypes.data_as(vp),
+             unif.ctypes.data_as(vp), N_INIT, n_trials, MIN_CENTER, float(max_corr), int(seed) & 0xFFFFFFFFFFFFFFFF,
+             int(n_hypotheses), int(bool(adaptive)), CONFIDENCE, out.ctypes.data_as(vp), ctx.stream)
+    status = int(out[34])
+    if status in (1, 2):
+        if status == 1 and rewind is not None:
+            src.set_state(rewind)
+        # the reference dereferences curr_model = None here (utils/symmetry.py:237)
+        why = "'NoneType' object has no attribute 'cluster_centers_'"
+    if why is not None:
         tqdm.write(f"symmetry failed use ransac: {why}")
-        A_perm = B_perm = None
-        q_off = r_off = maps = np.zeros(1, np.int32)
-        K, P = 0, 0
-    T_all = ctx.empty((1 + P, 4, 4), torch.float64)
-    chamf_d = ctx.empty((1 + P,), torch.float64)
-    ctx.call("cb_register_pairings", ptr(baseF_d), ptr(xyz0_d), n0, ptr(posF_d), ptr(xyz1_d), n1, d, int(k_nn),
-             ptr(A_perm), q_off.ctypes.data_as(_capi.c_void_p), ptr(B_perm), r_off.ctypes.data_as(_capi.c_void_p), K,
-             maps.ctypes.data_as(_capi.c_void_p), P, float(max_corr), int(seed) & 0xFFFFFFFFFFFFFFFF,
-             int(n_hypotheses), int(bool(adaptive)), CONFIDENCE, ptr(T_all), ptr(chamf_d), None, ctx.stream)
-    out = torch.cat([T_all.reshape(-1), chamf_d]).cpu().numpy()  # the one synchronisation of the sweep
-    Ts = torch.from_numpy(out[:16 * (1 + P)].reshape(1 + P, 4, 4).astype(np.float32))
-    chamf = out[16 * (1 + P):]
-    best = 0
-    for i in range(1, 1 + P):
-        if chamf[best] > chamf[i]:  # strictly lower Chamfer wins (:321,:353)
-            best = i
-    return Ts[best], float(chamf[best]), Ts[0], float(chamf[0]), ok
+    T = torch.from_numpy(out[:34].astype(np.float32))
+    return T[:16].reshape(4, 4), float(out[16]), T[17:33].reshape(4, 4), float(out[33]), why is None
 
 
 # ---------------------------------------------------------------------------------------------

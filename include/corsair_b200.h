@@ -234,6 +234,34 @@ int cb_register_pairings(cb_ctx* ctx, const float* base_f, const float* base_xyz
                          double max_dist, uint64_t seed, int h_total, int adaptive, double confidence,
                          double* T_out, double* chamfer_out, double* stats_out, void* stream);
 
+/* HOST ONLY, no device work: replays `rs = np.random.RandomState(seed)` followed by `count` successive
+ * `rs.choice(n[c], size, replace=False)` (legacy MT19937 seeding, Fisher-Yates permutation with the
+ * masked-rejection bounded draw) into out [count, size] int32.  CB_EINVAL when some n[c] < size
+ * (NumPy raises there). */
+int cb_np_seeded_choices(uint32_t seed, const int32_t* n, int count, int size, int32_t* out);
+
+/* ---- sym_pose end to end (utils/symmetry.py:262-358) ------------------------------------------
+ * One call per query-CAD pair: the vanilla registration, the symmetry segmentation of both clouds
+ * (symmetric_cut4 with K = 4 when pos_sym >= 2, else 2: :289-298) and, when both accept a model,
+ * every pairing of the sweeps (:303-356).  The 1 + P registrations are independent and run on a
+ * few internal streams (CB_SYM_STREAMS, default 3; 0 = all on `stream`); the call returns after its
+ * results are on the host.  Device inputs as for cb_register_pairings.
+ * HOST inputs: h_samples_base / h_samples_pos [n_samples] int32 — the seed rows the caller drew with
+ * choice(n, 100, replace=False) (:193; n_samples = 0 skips the segmentation) — or both NULL with
+ * np_seed in [0, 2^32): the call draws them itself as np.random.seed(np_seed) followed by the two
+ * choices would (cb_np_seeded_choices); h_km_first [n_init]
+ * int32 and h_km_unif [n_init, K-1, n_trials] float64 — the data-independent RandomState(0) draws of
+ * sklearn's k-means++ (cb_kmeans_batch).
+ * h_out [40] float64 (HOST): [0,16) best pose (float32 values), [16] its Chamfer distance, [17,33)
+ * the vanilla pose, [33] its Chamfer distance, [34] status (0 symmetry search ran; 1 / 2 the base /
+ * pos segmentation accepted no model — the reference raises and falls back, :299-301; 3 not
+ * attempted), [35] index of the winning registration (0 vanilla), [36] pairings evaluated. */
+int cb_sym_pose(cb_ctx* ctx, const float* base_f, const float* base_xyz, int n0, const float* pos_f,
+                const float* pos_xyz, int n1, int d, int pos_sym, int k_nn, const int32_t* h_samples_base,
+                const int32_t* h_samples_pos, int n_samples, int64_t np_seed, int n_nn, const int32_t* h_km_first,
+                const double* h_km_unif, int n_init, int n_trials, double min_center, double max_dist,
+                uint64_t seed, int h_total, int adaptive, double confidence, double* h_out, void* stream);
+
 /* ---- K5: IRLS pose (utils/_transform_estimation.py:110-137) ------------------------------
  * est_quad_linear_robust: iters (reference: 20) iterations of the linearised weighted solve.
  * p0,p1 [n,3] float32, w [n] float32 (NULL = ones); T [16] float32 (device). */

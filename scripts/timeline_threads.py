@@ -61,6 +61,18 @@ def main():
         a[1] += e["dur"]
     for n, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]:
         print(f"  {d/steps/1e3:8.3f} ms/step  {c/steps:7.1f} launches/step  avg {d/c:7.1f} us  {n}")
+    # idle gaps: where in the run, how long, and which kernels sit on either side
+    evs = sorted(ev, key=lambda e: e["ts"])
+    gaps, end, last = [], None, None
+    for e in evs:
+        if end is not None and e["ts"] > end:
+            gaps.append((e["ts"] - end, end - evs[0]["ts"], last["name"][:40], e["name"][:40]))
+        if end is None or e["ts"] + e["dur"] > end:
+            end, last = e["ts"] + e["dur"], e
+    print(f"idle gaps: {len(gaps)} totalling {sum(g[0] for g in gaps)/steps/1e3:.2f} ms/step; "
+          f"{sum(1 for g in gaps if g[0] > 100)} above 100 us = {sum(g[0] for g in gaps if g[0] > 100)/steps/1e3:.2f} ms/step")
+    for g in sorted(gaps, key=lambda g: -g[0])[:24]:
+        print(f"  {g[0]:8.1f} us at t={g[1]/1e3:8.2f} ms   after {g[2]:40s} before {g[3]}")
     os.remove(path)
 
 

@@ -72,3 +72,23 @@ def test_dropin_install_aliases_reference_module_names():
         m = sys.modules["utils_dropin_test." + mod]
         for n in names:
             assert callable(getattr(m, n)), f"{mod}.{n}"
+
+
+def test_np_seeded_choices_replays_numpy():
+    """cb_np_seeded_choices (host only) against NumPy's legacy RandomState: the seed rows symmetric_cut4
+    draws (utils/symmetry.py:193) must be the same whether Python or the C call draws them."""
+    import numpy as np
+    from corsair_b200 import _capi
+    f = _capi.load_library().cb_np_seeded_choices
+    for seed in (0, 1, 31, 20260101, 2 ** 32 - 1):
+        for ns in ([4096, 3000], [100, 100, 101], [2048], [70000, 257], [1]):
+            size = min(100, min(ns))
+            n = np.asarray(ns, np.int32)
+            out = np.full((len(ns), size), -1, np.int32)
+            assert f(seed, n.ctypes.data, len(ns), size, out.ctypes.data) == 0
+            rs = np.random.RandomState(seed)
+            for i, k in enumerate(ns):
+                assert np.array_equal(rs.choice(k, size, replace=False), out[i]), (seed, ns, i)
+    n = np.asarray([4096, 99], np.int32)
+    out = np.zeros((2, 100), np.int32)
+    assert f(3, n.ctypes.data, 2, 100, out.ctypes.data) != 0  # NumPy raises: sample larger than population

@@ -202,3 +202,53 @@ def test_sym_pose_many_matches_sequential(ctx):
         for x in (b, c):
             assert np.array_equal(a[0].numpy(), x[0].numpy()) and np.array_equal(a[2].numpy(), x[2].numpy())
             assert a[1] == x[1] and a[3] == x[3] and a[4] == x[4]
+
+
+@pytest.mark.parametrize("category", ["chair", "table"])
+def test_sym_pose_int_seed_and_streams(ctx, category, monkeypatch):
+    """rng=<int> (seed rows replayed in C) equals rng=RandomState(<int>) equals np.random.seed(<int>),
+    and cb_sym_pose gives the same result from cb_register_pairings' single-stream composition
+    (segments -> pairings, as tests above pin against the oracle)."""
+    from corsair_b200 import symmetry, synth
+    from corsair_b200._capi import ptr
+    p = synth.make_pair(41, 32, category, n_raw=3000)
+    args = (p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"])
+    kw = dict(k_nn=5, max_corr=0.2, seed=9, n_hypotheses=30000)
+    a = symmetry.sym_pose(*args, rng=17, **kw)
+    b = symmetry.sym_pose(*args, rng=np.random.RandomState(17), **kw)
+    np.random.seed(17)
+    c = symmetry.sym_pose(*args, **kw)
+    for x in (b, c):
+        assert torch.equal(a[0], x[0]) and torch.equal(a[2], x[2]) and a[1] == x[1] and a[3] == x[3] and a[4] == x[4]
+    assert a[4] is True
+
+    # the same pair composed from the separately tested pieces on ONE stream
+    K = 4 if p["pos_sym"] >= 2 else 2
+    fd = [ctx.dev(v, torch.float32) for v in args[:4]]
+    rs = np.random.RandomState(17)
+    A_perm, offA = symmetry._segments_device(fd[0], fd[1], K, 100, ctx, rs)
+    B_perm, offB = symmetry._segments_device(fd[2], fd[3], K, 100, ctx, rs)
+    off = torch.stack([offA, offB]).cpu().numpy()
+    assert off[0, K + 1] >= 0 and off[1, K + 1] >= 0
+    maps = symmetry._pair_maps(K, p["pos_sym"] >= 2)
+    P = len(maps)
+    T_all, ch = ctx.empty((1 + P, 4, 4), torch.float64), ctx.empty((1 + P,), torch.float64)
+    q_off, r_off = np.ascontiguousarray(off[0, :K + 1]), np.ascontiguousarray(off[1, :K + 1])
+    ctx.call("cb_register_pairings", ptr(fd[0]), ptr(fd[1]), len(p["xyz0"]), ptr(fd[2]), ptr(fd[3]), len(p["xyz1"]), 32, 5,
+             ptr(A_perm), q_off.ctypes.data, ptr(B_perm), r_off.ctypes.data, K, maps.ctypes.data, P, 0.2, 9, 30000, 1,
+             symmetry.CONFIDENCE, ptr(T_all), ptr(ch), None, ctx.stream)
+    T_all, ch = T_all.cpu().numpy(), ch.cpu().numpy()
+    best = 0
+    for i in range(1, 1 + P):
+        if ch[best] > ch[i]:
+            best = i
+    assert np.array_equal(T_all[best].astype(np.float32), a[0].numpy()) and ch[best] == a[1]
+    assert np.array_equal(T_all[0].astype(np.float32), a[2].numpy()) and ch[0] == a[3]
+
+
+def test_sym_pose_int_seed_small_cloud_falls_back(ctx, rng):
+    from corsair_b200 import symmetry
+    F0 = rng.standard_normal((60, 16)).astype(np.float32)
+    x0 = rng.standard_normal((60, 3)).astype(np.float32)
+    out = symmetry.sym_pose(F0, x0, F0.copy(), x0.copy(), 1, k_nn=5, max_corr=0.2, seed=0, rng=5)
+    assert out[4] is False and torch.equal(out[0], out[2]) and out[1] == out[3]
