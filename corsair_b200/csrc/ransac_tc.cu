@@ -20,6 +20,8 @@
 //           The kernel is bound by this drain: tensor memory reads at 64 B/clk/SM = 16 evaluations/clk/SM
 #include "ransac_internal.cuh"
 
+#include <stdlib.h>
+
 #include <math.h>
 
 namespace {
@@ -177,7 +179,7 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
     }
 }
 
-template <bool DUMP>
+template <bool DUMP, int LDW = 32>
 __global__ void __launch_bounds__(kThreads, 1)
 ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
                        const float* __restrict__ band_g, const double* __restrict__ Tw,
@@ -314,14 +316,25 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
             c2 = pk2(0.f, 0.f);
             s2 = pk2(0.f, 0.f);
-            // drain this thread's columns, 32 at a time (measured: neither double-buffering the loads
-            // nor 16 epilogue warps beats this; the tensor-memory read rate is the limit)
+            // drain this thread's columns, 64 (or 32) at a time (measured: neither double-buffering the
+            // loads nor 16 epilogue warps beats this; the tensor-memory read rate is the limit)
+            if constexpr (LDW == 64) {
 #pragma unroll 1
-            for (int k = 0; k < kChunks; ++k) {
-                float v[32];
-                tc::tmem_ld32(taddr + k * 32, v);
-                tc::tmem_ld_wait();
-                process(v, col0 + k * 32);
+                for (int k = 0; k < kChunks; k += 2) {
+                    float v[64];
+                    tc::tmem_ld64(taddr + k * 32, v);
+                    tc::tmem_ld_wait();
+                    process(*reinterpret_cast<const float(*)[32]>(v), col0 + k * 32);
+                    process(*reinterpret_cast<const float(*)[32]>(v + 32), col0 + k * 32 + 32);
+                }
+            } else {
+#pragma unroll 1
+                for (int k = 0; k < kChunks; ++k) {
+                    float v[32];
+                    tc::tmem_ld32(taddr + k * 32, v);
+                    tc::tmem_ld_wait();
+                    process(v, col0 + k * 32);
+                }
             }
             // accumulator stage drained: hand it back to the MMA warp
             tc::fence_before_sync();
@@ -411,10 +424,12 @@ int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_b
                 Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps,
                 dump + (size_t)h0 * dump_ld, dump_ld);
     } else {
-        e = cudaFuncSetAttribute(ransac_tc_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)kScoreSmem);
+        // 64-column tcgen05.ld: 650 vs 664 us per 100 000 x 16 345 registration (CB_RT_LD64=0: 32 columns)
+        static const bool ld64 = !(getenv("CB_RT_LD64") && !atoi(getenv("CB_RT_LD64")));
+        auto kern = ld64 ? ransac_tc_score_kernel<false, 64> : ransac_tc_score_kernel<false, 32>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
         if (e == cudaSuccess)
-            ransac_tc_score_kernel<false><<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
+            kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
                 Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps, nullptr, 0);
     }
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "ransac_tc_score_kernel: %s", cudaGetErrorString(e));

@@ -248,5 +248,7 @@ def sym_pose_many(jobs, workers=4):
     device = torch.cuda.current_device()
     ready = torch.cuda.Event()
     ready.record(torch.cuda.current_stream(device))
-    futs = [_pool.submit(_worker_run, device, ready, a, k) for a, k in jobs]
-    return [f.result() for f in futs]
+    # longest first: a pair with pos_sym >= 2 runs 9 registrations, the others 3 (utils/symmetry.py:303-356)
+    order = sorted(range(len(jobs)), key=lambda i: 0 if jobs[i][0][4] >= 2 else 1)
+    futs = {i: _pool.submit(_worker_run, device, ready, *jobs[i]) for i in order}
+    return [futs[i].result() for i in range(len(jobs))]

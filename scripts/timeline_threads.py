@@ -61,6 +61,29 @@ def main():
         a[1] += e["dur"]
     for n, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]:
         print(f"  {d/steps/1e3:8.3f} ms/step  {c/steps:7.1f} launches/step  avg {d/c:7.1f} us  {n}")
+    # how much of the busy time has a scoring kernel resident, and what runs when none is
+    def union(ivs):
+        tot, cs, ce = 0.0, None, None
+        for a, b in sorted(ivs):
+            if ce is None or a > ce:
+                if ce is not None:
+                    tot += ce - cs
+                cs, ce = a, b
+            else:
+                ce = max(ce, b)
+        return tot + (ce - cs if ce is not None else 0.0)
+    sc = [(e["ts"], e["ts"] + e["dur"]) for e in ev if "ransac_tc_score" in e["name"]]
+    print(f"scoring kernel resident (union) {union(sc)/steps/1e3:.2f} ms/step of {busy/steps/1e3:.2f} busy; "
+          f"alone it sums to {sum(b - a for a, b in sc)/steps/1e3:.2f} ms/step")
+    # time with k scoring kernels in flight
+    pts = sorted([(a, 1) for a, b in sc] + [(b, -1) for a, b in sc])
+    hist, k, last_t = {}, 0, None
+    for t, dlt in pts:
+        if last_t is not None:
+            hist[k] = hist.get(k, 0.0) + t - last_t
+        k += dlt
+        last_t = t
+    print("  scoring kernels in flight: " + ", ".join(f"{k}: {v/steps/1e3:.2f} ms" for k, v in sorted(hist.items())))
     # idle gaps: where in the run, how long, and which kernels sit on either side
     evs = sorted(ev, key=lambda e: e["ts"])
     gaps, end, last = [], None, None
