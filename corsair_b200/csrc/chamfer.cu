@@ -82,14 +82,15 @@ nn3_finalize_kernel(const float* __restrict__ p, int np, const double* __restric
 
 // out[0] (+)= sum(partials)/n   or   max(partials)
 __global__ void nn3_reduce_kernel(const double* __restrict__ partial_sum, const double* __restrict__ partial_max,
-                                  int nblocks, int n, int mode /*0 mean set,1 mean add,2 max*/,
+                                  int nblocks, int n, int mode /*0 mean set,1 mean add,2 max set,3 max of both*/,
                                   double* __restrict__ out) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double s = 0.0, m = 0.0;
     for (int b = 0; b < nblocks; ++b) { s += partial_sum[b]; m = fmax(m, partial_max[b]); }
     if (mode == 0) out[0] = s / (double)n;
     else if (mode == 1) out[0] += s / (double)n;
-    else out[0] = m;
+    else if (mode == 2) out[0] = m;
+    else out[0] = fmax(out[0], m);
 }
 
 __global__ void pack_points_dev_pose_kernel(const float* __restrict__ xyz, int n, const double* __restrict__ T,
@@ -140,7 +141,7 @@ static int chamfer_impl(cb_ctx* ctx, const float* a, int na, const float* b, int
     CB_LAUNCH_CHECK(ctx);
     rc = nn3_direction(ctx, a, na, T, a4, b, nb, nullptr, b4, use_max ? 2 : 0, out, nn_idx, st);
     if (rc) return rc;
-    if (two_dir) rc = nn3_direction(ctx, b, nb, nullptr, b4, a, na, T, a4, 1, out, nullptr, st);
+    if (two_dir) rc = nn3_direction(ctx, b, nb, nullptr, b4, a, na, T, a4, use_max ? 3 : 1, out, nullptr, st);
     return rc;
 }
 
@@ -162,4 +163,20 @@ extern "C" int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, in
     int rc = cb_begin(ctx);
     if (rc) return rc;
     return chamfer_impl(ctx, a, na, b, nb, T, 0, 1, out, nullptr, (cudaStream_t)stream);
+}
+
+// chamfer_max of a cloud against rigidly moved copies of itself (evaluation-shapenet.py:122-146):
+// out[r] = max over BOTH directions of the nearest-neighbour distance between xyz and T_r(xyz).
+extern "C" int cb_self_hausdorff(cb_ctx* ctx, const float* xyz, int n, const double* T, int n_poses, double* out,
+                                 void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    if (n_poses == 0) return CB_OK;
+    if (!xyz || !T || !out || n <= 0 || n_poses < 0) CB_FAIL(ctx, CB_EINVAL, "cb_self_hausdorff: bad arguments");
+    for (int r = 0; r < n_poses; ++r) {
+        ctx->arena_off = 0;  // the stream orders the poses: each reuses the scratch of the one before
+        if ((rc = chamfer_impl(ctx, xyz, n, xyz, n, T + 16 * (size_t)r, 1, 1, out + r, nullptr, (cudaStream_t)stream)))
+            return rc;
+    }
+    return CB_OK;
 }

@@ -181,6 +181,13 @@ int cb_chamfer_matrix(cb_ctx* ctx, const float* pts, int L, int P, int row0, int
 int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
               double* out, void* stream);
 
+/* chamfer_max of a cloud against moved copies of itself — the test behind get_symmetry_label
+ * (evaluation-shapenet.py:122-155): for each of n_poses rigid poses T [n_poses,16] float64 (DEVICE,
+ * row-major 4x4), out[r] (DEVICE float64) = max over both directions of the nearest-neighbour distance
+ * between xyz [n,3] and T_r applied to xyz. */
+int cb_self_hausdorff(cb_ctx* ctx, const float* xyz, int n, const double* T, int n_poses, double* out,
+                      void* stream);
+
 /* ---- K3': symmetric_cut4 pieces (utils/symmetry.py:182-259) -------------------------------
  * feature rows + 50-NN (:201-214): for each of n_samples rows sample_idx[s] of feat [n,d], the
  * n_nn nearest rows (itself included) as ASCENDING row indices: nn_idx [n_samples,n_nn] int32. */

@@ -132,3 +132,18 @@ def test_ransac_restatements_agree():
     # degenerate requests return Open3D's default result
     r = ransac_c.ransac(s[:5], t[:5], 0.2, ms[:4] % 5, adaptive=False)
     assert r["best_h"] == -1 and np.array_equal(r["T"], np.eye(4))
+
+
+def test_shapenet_symmetry_label():
+    """oracle/port_shapenet.py against vectors produced by the reference's own source
+    (evaluation-shapenet.py:122-154, tests/golden/make_shapenet_golden.py)."""
+    from oracle import port_shapenet as ps
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "shapenet.npz"))
+    n = len(g["labels"])
+    assert sorted(set(g["labels"].tolist())) == [1, 2, 3, 4, 6, 8, 12]
+    for c in range(n):
+        pc = g[f"pc{c}"]
+        assert ps.get_symmetry_label(pc, float(g["threshold"])) == g["labels"][c]
+        errs = [e for sym in ps.SYM_ORDERS for e in ps.rotation_errors(sym, pc)]
+        np.testing.assert_allclose(errs, g["errors"][c], rtol=0, atol=1e-12)
+        assert ps.test_symmetry_label(4, pc, 0.05) == bool(g["test_label4_thr005"][c])
