@@ -286,6 +286,29 @@ def run_ours(args, rank, world, local_rank):
     shares = {k: {"ms": round(v[0], 3), "launches": v[2], "share_of_tracked": round(v[0] / max(total_tracked, 1e-9), 4)}
               for k, v in tracked.items()}
 
+    # the metric's second half: the feature-kNN distance GEMM against the split-precision tensor peak, on
+    # the largest single-pair shape BASELINE.json names (configs[4]: 50k-point scan vs a 10k-point CAD)
+    from corsair_b200 import find_nn
+    g = torch.Generator(device=dev).manual_seed(5)
+    fa = torch.nn.functional.normalize(torch.randn(50000, D_FEAT, device=dev, generator=g), dim=1)
+    fb = torch.nn.functional.normalize(torch.randn(10000, D_FEAT, device=dev, generator=g), dim=1)
+    for _ in range(3):
+        find_nn.knn_device(fa, fb, K_NN)
+    ke0, ke1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ke0.record()
+    for _ in range(10):
+        find_nn.knn_device(fa, fb, K_NN)
+    ke1.record()
+    torch.cuda.synchronize()
+    knn_tf = 2.0 * 50000 * 10000 * D_FEAT / (ke0.elapsed_time(ke1) / 10 * 1e-3) / 1e12
+    knn_tensor = {"shape": f"50000 x 10000, D = {D_FEAT}, k = {K_NN}", "achieved": knn_tf, "unit": "TFLOP/s",
+                  "peak": bf16 / 3.0, "frac": knn_tf / (bf16 / 3.0), "us_per_call": ke0.elapsed_time(ke1) / 10 * 1e3,
+                  "note": "whole cb_knn call (norms, packing, two-pass tcgen05 candidate kernel, exact re-rank), 2*N0*N1*D "
+                          f"flop; peak = {src} sustained bf16 dense / 3 products.  Every score is read out of tensor "
+                          "memory twice (64 B/clk/SM), which caps this at 32 % of that peak (DESIGN.md K1)"}
+    del fa, fb
+
     cpu_base = None
     if world == 1:
         from oracle import ransac_c
@@ -301,7 +324,10 @@ def run_ours(args, rank, world, local_rank):
 
     h2d = nbytes(queries[0]["desc"]) + TOPK * (nbytes(queries[0]["F"], queries[0]["xyz"]) +
                                                int(np.mean([nbytes(c["F"], c["xyz"]) for c in cads]))) + nbytes(lib)
-    d2h = TOPK * 8 * 2 + TOPK * (2 * 64 + 16 + 2 * 400 * 8 + 3 * 8 * 4)
+    # per pair: the two seed-row draws and k-means++ draws go up (cb_sym_pose's staging), the segment
+    # offsets and the 1 + P poses / Chamfer values come back
+    h2d += TOPK * (2 * 100 * 4 + 10 * 4 + 10 * 1 * 2 * 8)
+    d2h = TOPK * 8 * 2 + TOPK * (16 * 4 + 3 * 17 * 8)
     print(json.dumps({
         "metric": "query-CAD pairs registered/sec", "value": value, "unit": "pairs/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
@@ -314,7 +340,8 @@ def run_ours(args, rank, world, local_rank):
                    "sequential_ms_per_step": ms_seq / n_inst, "sharding": f"queries sharded over {world} rank(s), no data-path collective"},
         "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "roofline": roof, "kernel_classes": shares, "cpu_baseline": cpu_base,
+        "gpu_launches": launches, "roofline": roof, "knn_tensor": knn_tensor, "kernel_classes": shares,
+        "cpu_baseline": cpu_base,
         "clocks": clocks}))
 
 

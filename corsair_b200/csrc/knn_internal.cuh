@@ -9,7 +9,7 @@
 
 // tcgen05 candidate pass (knn_tc.cu), d in {16,32}, KC in {8,16}, LC = 3 KC: every reference of the
 // chunk whose score is at or below the chunk's threshold (the KC-th best of its column-group minima,
-// so at least KC references qualify), in column order; bound[qi*S + c] = that threshold (no dropped
+// so at least KC references qualify), in no particular order; bound[qi*S + c] = that threshold (no dropped
 // reference scores below it), -inf when more than LC qualified (the re-rank then sends the row to
 // the exact fallback).
 int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr,

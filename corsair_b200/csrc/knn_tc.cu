@@ -10,11 +10,15 @@
 // knn.cu).  Error: |dot' - exact| <= 3*2^-18 |q||r| + fp32 accumulation, covered by
 // knn_cand_tc_gamma() in the re-rank's proof obligation.
 //
-// Pipeline per CTA (one 128-query tile x one reference chunk), 192 threads:
-//   warp 4  producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
-//   warp 5  one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
+// Pipeline per CTA (one 128-query tile x one reference chunk), 320 threads:
+//   warp 8  producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
+//   warp 9  one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
 //           of two 256-column TMEM accumulators and commits to mbarriers
-//   warps 0-3 epilogue: one query row (TMEM lane) per thread, tcgen05.ld 32 columns at a time.
+//   warps 0-7 epilogue: warp w drains lane quadrant w%4 (one query row per thread), column half w/4
+//           of every accumulator, tcgen05.ld 32 columns at a time — two warps per SM sub-partition,
+//           so one warp's tensor-memory load overlaps the other's arithmetic.  The two threads of a
+//           row merge their pass-1 lists through shared memory (same threshold as one thread over
+//           all columns would find) and share the row's candidate list through a shared counter.
 // The chunk's GEMM runs TWICE (the tensor pipe is nearly idle, the operands sit in L2):
 //   pass 1  per row, the maxima of column groups (16 or 8 columns) go through a branch-free
 //           sorted insertion into the row's KC best group maxima; their KC-th is the row's
@@ -35,9 +39,14 @@ namespace {
 constexpr int kTileM = 128;   // queries per CTA (TMEM lanes)
 constexpr int kTileN = 256;   // references per MMA / accumulator stage
 constexpr int kExtraK = 16;   // the norm block of the widened K axis
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (kEpiWarps + 2) * 32;
 
 __host__ __device__ constexpr int kprime(int D) { return 3 * D + kExtraK; }
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 
 // fp32 rows [n, D] -> packed bf16 operand tiles.  One thread per (row, 8-column group).
 // is_b: 0 = A layout (hi|hi|lo|ones), 1 = B layout (hi|lo|hi|-norm/2 split in three).
@@ -102,6 +111,8 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
     unsigned char* sA = smem;
     unsigned char* sB = smem + A_BYTES;
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + 2 * B_BYTES);
+    float* s_top = reinterpret_cast<float*>(smem + A_BYTES + 2 * B_BYTES + 128);  // [2][kTileM][KC]
+    int* s_cnt = reinterpret_cast<int*>(s_top + 2 * kTileM * KC);                // [kTileM]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c = blockIdx.y;
     const int t0 = (c * chunk) / kTileN;
@@ -115,17 +126,18 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             tc::mbar_init(&ctl->full[i], 1);
             tc::mbar_init(&ctl->empty[i], 1);
             tc::mbar_init(&ctl->tmem_full[i], 1);
-            tc::mbar_init(&ctl->tmem_empty[i], 4);
+            tc::mbar_init(&ctl->tmem_empty[i], kEpiWarps);
         }
         tc::fence_barrier_init();
     }
-    if (warp == 4) tc::tmem_alloc(&ctl->tmem_base, 512);
+    if (threadIdx.x < kTileM) s_cnt[threadIdx.x] = 0;
+    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 512);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tbase = ctl->tmem_base;
 
-    if (warp == 4) {
+    if (warp == kEpiWarps) {
         // ===== producer: bulk copies of pre-packed tiles =====
         if (lane == 0) {
             tc::mbar_arrive_expect_tx(&ctl->a_full, A_BYTES);
@@ -139,7 +151,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                              &ctl->full[st]);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kEpiWarps + 1) {
         // ===== MMA issuer: one thread =====
         if (lane == 0) {
             constexpr uint32_t idesc = tc::idesc_bf16(kTileM, kTileN);
@@ -162,27 +174,45 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             }
         }
     } else {
-        // ===== epilogue: 128 threads, one query row (TMEM lane) each =====
-        const int row = threadIdx.x;
+        // ===== epilogue: 256 threads = 128 query rows (TMEM lanes) x 2 column halves =====
+        const int half = warp >> 2;
+        const int row = (warp & 3) * 32 + lane;
         const int qi = blockIdx.x * kTileM + row;
         const size_t o = ((size_t)min(qi, nq - 1) * S + c) * LC;
         const bool live = qi < nq;
-        float top[KC];  // the KC best group maxima, descending
+        constexpr int kHalfN = kTileN / 2;
+        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + half * kHalfN;
+        float top[KC];  // the KC best group maxima of this thread's columns, descending
 #pragma unroll
         for (int t = 0; t < KC; ++t) top[t] = -INFINITY;
         float tau = -INFINITY;
-        int cnt = 0;
         for (int it = 0; it < nsteps; ++it) {
             const int st = it & 1, use = it >> 1;
             const bool second = it >= ntiles;
+            if (it == ntiles) {
+                // the row's threshold: KC-th best of the union of both halves' group maxima
+#pragma unroll
+                for (int t = 0; t < KC; ++t) s_top[(half * kTileM + row) * KC + t] = top[t];
+                named_bar_sync(1, kEpiWarps * 32);
+#pragma unroll
+                for (int u = 0; u < KC; ++u) {
+                    float x = s_top[((half ^ 1) * kTileM + row) * KC + u];
+#pragma unroll
+                    for (int t = 0; t < KC; ++t) {
+                        const float hi = fmaxf(top[t], x);
+                        x = fminf(top[t], x);
+                        top[t] = hi;
+                    }
+                }
+                tau = fmaxf(top[KC - 1], -1e29f);  // padding (-1e30) never qualifies
+            }
             tc::mbar_wait(&ctl->tmem_full[st], use & 1);
             tc::fence_after_sync();
-            const int col0 = (t0 + (second ? it - ntiles : it)) * kTileN;
-            if (it == ntiles) tau = fmaxf(top[KC - 1], -1e29f);  // padding (-1e30) never qualifies
+            const int col0 = (t0 + (second ? it - ntiles : it)) * kTileN + half * kHalfN;
 #pragma unroll 1
-            for (int cb = 0; cb < kTileN / 32; ++cb) {
+            for (int cb = 0; cb < kHalfN / 32; ++cb) {
                 float v[32];
-                tc::tmem_ld32(tbase + ((uint32_t)(warp * 32) << 16) + st * kTileN + cb * 32, v);
+                tc::tmem_ld32(lane_addr + st * kTileN + cb * 32, v);
                 tc::tmem_ld_wait();
                 if (!second) {
 #pragma unroll
@@ -205,15 +235,15 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                     for (int e = 0; e < 32; ++e) mask |= (v[e] >= tau ? 1u : 0u) << e;
                     // padding rows (all-equal scores) and rows whose list already overflowed (they go
                     // to the exact fallback whatever else qualifies) must not spin in the loop below
-                    if (!live || cnt > LC) mask = 0;
+                    if (!live || (mask && *(volatile int*)&s_cnt[row] > LC)) mask = 0;
                     // append their reference indices (the re-rank recomputes every candidate exactly,
                     // the approximate scores are not needed); ~1 % of the columns qualify
                     while (mask) {
                         const int e = __ffs(mask) - 1;
                         mask &= mask - 1;
-                        if (cnt < LC && live)
-                            cand_idx[o + cnt] = (int)(((unsigned long long)(col0 + cb * 32 + e) * perm_inv) % (unsigned)nr_pad);
-                        ++cnt;
+                        const int pos = atomicAdd(&s_cnt[row], 1);
+                        if (pos < LC)
+                            cand_idx[o + pos] = (int)(((unsigned long long)(col0 + cb * 32 + e) * perm_inv) % (unsigned)nr_pad);
                     }
                 }
             }
@@ -221,7 +251,9 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
         }
-        if (live) {
+        named_bar_sync(1, kEpiWarps * 32);  // both halves of every row have appended
+        if (live && half == 0) {
+            const int cnt = s_cnt[row];
             for (int t = min(cnt, LC); t < LC; ++t) cand_idx[o + t] = -1;
             // no dropped reference scores below the threshold; an overflowing list proves nothing
             bound[(size_t)qi * S + c] = cnt > LC ? -INFINITY : (maxdot ? -tau : -2.f * tau);
@@ -229,14 +261,14 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 4) tc::tmem_dealloc(tbase, 512);
+    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, 512);
 }
 
 template <int D, int KC>
 cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
                       unsigned perm_inv, int nr_pad, int32_t* ci, float* bound, cudaStream_t st) {
     constexpr int KP = kprime(D);
-    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + sizeof(TcSmemCtl) + 64;
+    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + 128 + 2 * kTileM * KC * 4 + kTileM * 4 + 64;
     cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((nq + kTileM - 1) / kTileM, S);
