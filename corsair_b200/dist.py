@@ -141,9 +141,11 @@ def ransac_sharded(src_xyz, tgt_xyz, max_corr_dist, seed=0, n_hypotheses=4096, *
 
 
 def chamfer_matrix_sharded(pcs):
-    """All-pairs Chamfer table (utils/pc_dist.py:61-99) with the rows split over ranks: every rank
-    computes its block of full rows on the device (cb_chamfer_matrix), one all-gather of the blocks
-    (padded to equal height).  Returns the [L,L] float64 table (diagonal 200 like the reference)."""
+    """All-pairs Chamfer table (utils/pc_dist.py:61-99) with the rows split over ranks.  Every rank
+    computes the circulant half of its rows on the device (cb_chamfer_matrix_half: each unordered pair
+    is computed exactly once across the ranks, the same number per row, so contiguous row blocks are
+    balanced), one all-gather of the blocks (padded to equal height), then H + H^T with the
+    reference's diagonal of 200.  Returns the [L,L] float64 table."""
     from . import pc_dist
     L = len(pcs)
     stack = torch.stack([p if isinstance(p, torch.Tensor) else torch.from_numpy(np.asarray(p)) for p in pcs]).float()
@@ -153,10 +155,12 @@ def chamfer_matrix_sharded(pcs):
     dev = torch.device("cuda", torch.cuda.current_device())
     block = torch.zeros((rows, L), dtype=torch.float64, device=dev)
     if hi > lo:
-        block[:hi - lo] = pc_dist.chamfer_rows_device(stack, lo, hi)
+        block[:hi - lo] = pc_dist.chamfer_rows_device(stack, lo, hi, half=True)
     allb = gather_rows(block).cpu().numpy()
-    out = np.empty((L, L), np.float64)
+    H = np.empty((L, L), np.float64)
     for r in range(ws):
         a, b = shard_range(L, r, ws)
-        out[a:b] = allb[r * rows:r * rows + (b - a)]
+        H[a:b] = allb[r * rows:r * rows + (b - a)]
+    out = H + H.T
+    out[np.arange(L), np.arange(L)] = 200.0
     return out

@@ -21,14 +21,16 @@ def compute_chamfer(base_idx, pc0, pcs, domain, table):
         table[base_idx, i] = chamfer(pc0, pcs[i])
 
 
-def chamfer_rows_device(pts, row0=0, row1=None, ctx=None):
-    """Rows [row0,row1) of the all-pairs table for a [L,P,3] stack -> [rows, L] float64 CUDA tensor."""
+def chamfer_rows_device(pts, row0=0, row1=None, ctx=None, half=False):
+    """Rows [row0,row1) of the all-pairs table for a [L,P,3] stack -> [rows, L] float64 CUDA tensor.
+    ``half``: only the circulant half of those rows (cb_chamfer_matrix_half: every unordered pair once
+    over all rows, zeros elsewhere) — what a row-sharded run computes before symmetrising."""
     ctx = ctx or _capi.get_context()
     p = ctx.dev(pts, torch.float32)
     L, P = p.shape[0], p.shape[1]
     row1 = L if row1 is None else row1
     out = ctx.empty((row1 - row0, L), torch.float64)
-    ctx.call("cb_chamfer_matrix", ptr(p), L, P, row0, row1, ptr(out), ctx.stream)
+    ctx.call("cb_chamfer_matrix_half" if half else "cb_chamfer_matrix", ptr(p), L, P, row0, row1, ptr(out), ctx.stream)
     return out
 
 

@@ -176,6 +176,14 @@ int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, cons
 int cb_chamfer_matrix(cb_ctx* ctx, const float* pts, int L, int P, int row0, int row1, double* out,
                       void* stream);
 
+/* The same table for row-sharded runs without redundant work: of rows row0..row1-1 only the entries
+ * of the circulant half are computed — row i owns the pairs (i, (i + t) mod L), t = 1 .. floor((L-1)/2),
+ * plus t = L/2 for i < L/2 when L is even — every unordered pair exactly once over all rows and the
+ * same number in every row; all other entries (diagonal included) are written as 0.  The full table
+ * is H + H^T with the diagonal set to 200 (corsair_b200/dist.py: chamfer_matrix_sharded).  P <= 4266. */
+int cb_chamfer_matrix_half(cb_ctx* ctx, const float* pts, int L, int P, int row0, int row1, double* out,
+                           void* stream);
+
 /* Hausdorff-style max of NN distances (evaluation-shapenet.py:122-155 chamfer_max), same
  * arguments as cb_chamfer one-direction; out [1] float64. */
 int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,

@@ -98,3 +98,29 @@ def test_retrieval_eval_and_get_rank(ctx, rng):
     r1, r2 = retrieval.retrieval_eval(lib, 0.1, table), port_retrieval.retrieval_eval(lib, 0.1, table)
     for key in r2:
         assert r1[key] == pytest.approx(r2[key], rel=1e-9)
+
+
+@pytest.mark.parametrize("L,P", [(7, 300), (8, 777), (3, 2048), (5, 1), (2, 4266)])
+def test_chamfer_table_half_and_ragged_sizes(ctx, rng, L, P):
+    """The packed-fp32 table kernel at point counts that are not multiples of its tiling, and the
+    circulant half used by row-sharded runs: H + H^T (+ diagonal) is the full table bit for bit, every
+    unordered pair appears exactly once, every row owns the same number of pairs (+-1 for even L)."""
+    from corsair_b200 import pc_dist
+    pts = np.stack([cloud(rng, P) if P > 1 else rng.standard_normal((1, 3)).astype(np.float32) for _ in range(L)])
+    full = pc_dist.chamfer_rows_device(pts).cpu().numpy()
+    ref = port_retrieval.compute_dist([torch.from_numpy(p) for p in pts])
+    np.testing.assert_allclose(full, ref, rtol=1e-5)
+    assert np.array_equal(full, full.T) and np.all(np.diag(full) == 200)
+    half = pc_dist.chamfer_rows_device(pts, half=True).cpu().numpy()
+    nz = half != 0
+    assert not (nz & nz.T).any() and (nz | nz.T | np.eye(L, dtype=bool)).all()
+    per_row = nz.sum(1)
+    assert per_row.max() - per_row.min() <= (1 if L % 2 == 0 else 0) and per_row.sum() == L * (L - 1) // 2
+    rebuilt = half + half.T
+    rebuilt[np.arange(L), np.arange(L)] = 200.0
+    assert np.array_equal(rebuilt, full)
+    # a row block of the half equals the same rows of the whole half; a row block of the full table
+    # (mirror entries inside the block written by one CTA) equals the same rows of the full table
+    if L >= 4:
+        assert np.array_equal(pc_dist.chamfer_rows_device(pts, 1, 3, half=True).cpu().numpy(), half[1:3])
+        assert np.array_equal(pc_dist.chamfer_rows_device(pts, 1, 4).cpu().numpy(), full[1:4])
