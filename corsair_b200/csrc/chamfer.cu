@@ -11,32 +11,95 @@
 
 #include <math.h>
 
-// brute-force NN: one x point per thread, y chunk tiled through shared memory; poses stay on the device
-__global__ void nn3_kernel(const float4* __restrict__ x, int nx, const float4* __restrict__ y, int ny,
-                           int chunk, unsigned long long* __restrict__ best) {
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 ch_pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void ch_unpk2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 ch_add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 ch_mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 ch_fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
+constexpr int kNnThreads = 256;
+constexpr int kNnPerThread = 4;  // x points per thread (two packed pairs)
+
+// brute-force NN: four x points per thread as two packed fp32 pairs (add/mul/fma.f32x2: two distances
+// per instruction), the y chunk tiled through shared memory as negated duplicated coordinates so that
+// p - v is one packed add; poses stay on the device.  The arithmetic per distance is the scalar
+// kernel's (dx*dx, then two fused multiply-adds), first minimum wins inside a chunk, (distance,
+// index) atomicMin across chunks.
+__global__ void __launch_bounds__(kNnThreads)
+nn3_kernel(const float4* __restrict__ x, int nx, const float4* __restrict__ y, int ny, int chunk,
+           unsigned long long* __restrict__ best) {
     constexpr int TY = 256;
-    __shared__ float4 sy[TY];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ float2 snx[TY], sny[TY], snz[TY];
+    const int i0 = blockIdx.x * (kNnThreads * kNnPerThread) + threadIdx.x;
     const int y0 = blockIdx.y * chunk, y1 = min(ny, y0 + chunk);
-    float4 p = i < nx ? x[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-    float bd = INFINITY;
-    int bj = 0;
+    f32x2 px[kNnPerThread / 2], py[kNnPerThread / 2], pz[kNnPerThread / 2];
+    float bd[kNnPerThread];
+    int bj[kNnPerThread];
+#pragma unroll
+    for (int k = 0; k < kNnPerThread / 2; ++k) {
+        const float4 a = x[min(i0 + (2 * k) * kNnThreads, nx - 1)];
+        const float4 b = x[min(i0 + (2 * k + 1) * kNnThreads, nx - 1)];
+        px[k] = ch_pk2(a.x, b.x);
+        py[k] = ch_pk2(a.y, b.y);
+        pz[k] = ch_pk2(a.z, b.z);
+        bd[2 * k] = bd[2 * k + 1] = INFINITY;
+        bj[2 * k] = bj[2 * k + 1] = 0;
+    }
     for (int base = y0; base < y1; base += TY) {
         const int nt = min(TY, y1 - base);
         __syncthreads();
-        if (threadIdx.x < nt) sy[threadIdx.x] = y[base + threadIdx.x];
+        if (threadIdx.x < nt) {
+            const float4 v = y[base + threadIdx.x];
+            snx[threadIdx.x] = make_float2(-v.x, -v.x);
+            sny[threadIdx.x] = make_float2(-v.y, -v.y);
+            snz[threadIdx.x] = make_float2(-v.z, -v.z);
+        }
         __syncthreads();
-#pragma unroll 8
+#pragma unroll 4
         for (int j = 0; j < nt; ++j) {
-            float4 v = sy[j];
-            float dx = p.x - v.x, dy = p.y - v.y, dz = p.z - v.z;
-            float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-            if (d < bd) { bd = d; bj = base + j; }
+            const f32x2 vx = *reinterpret_cast<const f32x2*>(&snx[j]);
+            const f32x2 vy = *reinterpret_cast<const f32x2*>(&sny[j]);
+            const f32x2 vz = *reinterpret_cast<const f32x2*>(&snz[j]);
+            const int jj = base + j;
+#pragma unroll
+            for (int k = 0; k < kNnPerThread / 2; ++k) {
+                const f32x2 dx = ch_add2(px[k], vx), dy = ch_add2(py[k], vy), dz = ch_add2(pz[k], vz);
+                const f32x2 d = ch_fma2(dz, dz, ch_fma2(dy, dy, ch_mul2(dx, dx)));
+                float d0, d1;
+                ch_unpk2(d, d0, d1);
+                if (d0 < bd[2 * k]) { bd[2 * k] = d0; bj[2 * k] = jj; }
+                if (d1 < bd[2 * k + 1]) { bd[2 * k + 1] = d1; bj[2 * k + 1] = jj; }
+            }
         }
     }
-    if (i < nx && y1 > y0) {
-        unsigned long long key = ((unsigned long long)__float_as_uint(bd) << 32) | (unsigned int)bj;
-        atomicMin(&best[i], key);
+    if (y1 > y0) {
+#pragma unroll
+        for (int k = 0; k < kNnPerThread; ++k) {
+            const int i = i0 + k * kNnThreads;
+            if (i < nx) {
+                unsigned long long key = ((unsigned long long)__float_as_uint(bd[k]) << 32) | (unsigned int)bj[k];
+                atomicMin(&best[i], key);
+            }
+        }
     }
 }
 
@@ -111,13 +174,14 @@ static int nn3_direction(cb_ctx* ctx, const float* p, int np, const double* Tp, 
     double* pm = cb_alloc_t<double>(ctx, nblk);
     if (!best || !ps || !pm) return CB_ENOMEM;
     CB_CUDA(ctx, cudaMemsetAsync(best, 0xff, (size_t)np * 8, st));
-    int S = cb_div_up(2 * ctx->sm_count, nblk);
+    const int nblk_nn = cb_div_up(np, kNnThreads * kNnPerThread);
+    int S = cb_div_up(4 * ctx->sm_count, nblk_nn);  // ~4 resident CTAs per SM
     S = max(1, min(S, cb_div_up(nq, 256)));
     int chunk = cb_div_up(cb_div_up(nq, S), 256) * 256;
     S = cb_div_up(nq, chunk);
     {
         cb_timed_scope ts(ctx, CB_T_CHAMFER_NN, 8.0 * np * (double)nq, st);
-        nn3_kernel<<<dim3(nblk, S), 256, 0, st>>>(p4, np, q4, nq, chunk, best);
+        nn3_kernel<<<dim3(nblk_nn, S), kNnThreads, 0, st>>>(p4, np, q4, nq, chunk, best);
         CB_LAUNCH_CHECK(ctx);
     }
     nn3_finalize_kernel<<<nblk, 256, 0, st>>>(p, np, Tp, q, Tq, best, ps, pm, nn_idx);
