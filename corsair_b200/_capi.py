@@ -56,6 +56,7 @@ SIGNATURES = {
     "cb_chamfer_matrix": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cb_chamfer_matrix_half": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cb_self_hausdorff": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "cb_chamfer_cross": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "cb_nn_max": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "cb_feature_rows_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                      c_void_p, c_void_p]),

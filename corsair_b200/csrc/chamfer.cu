@@ -244,3 +244,24 @@ extern "C" int cb_self_hausdorff(cb_ctx* ctx, const float* xyz, int n, const dou
     }
     return CB_OK;
 }
+
+// Cross table of two-direction Chamfer distances between two stacks of equal-sized clouds — the
+// GT-CAD x reconstruction table of utils/precompute_chamfer_splats.py:113-149 (15 000 points each
+// there): out[i, j] = chamfer_kdtree_1direction(A_i, B_j) + chamfer_kdtree_1direction(B_j, A_i).
+// One pair Chamfer per entry on the stream; at that size each is ~200 us of search work, so the
+// launches are not the limit.
+extern "C" int cb_chamfer_cross(cb_ctx* ctx, const float* a, int la, int pa, const float* b, int lb, int pb,
+                                double* out, void* stream) {
+    int rc = cb_begin(ctx);
+    if (rc) return rc;
+    if (la == 0 || lb == 0) return CB_OK;
+    if (!a || !b || !out || la < 0 || lb < 0 || pa <= 0 || pb <= 0) CB_FAIL(ctx, CB_EINVAL, "cb_chamfer_cross: bad arguments");
+    for (int i = 0; i < la; ++i)
+        for (int j = 0; j < lb; ++j) {
+            ctx->arena_off = 0;  // stream order makes the scratch reusable pair after pair
+            if ((rc = chamfer_impl(ctx, a + (size_t)i * pa * 3, pa, b + (size_t)j * pb * 3, pb, nullptr, 1, 0,
+                                   out + (size_t)i * lb + j, nullptr, (cudaStream_t)stream)))
+                return rc;
+        }
+    return CB_OK;
+}

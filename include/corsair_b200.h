@@ -184,6 +184,12 @@ int cb_chamfer_matrix(cb_ctx* ctx, const float* pts, int L, int P, int row0, int
 int cb_chamfer_matrix_half(cb_ctx* ctx, const float* pts, int L, int P, int row0, int row1, double* out,
                            void* stream);
 
+/* Cross table of two-direction Chamfer distances (utils/precompute_chamfer_splats.py:113-149, the
+ * table evaluation-scan2cad.py:311-317 reads back): a [la,pa,3], b [lb,pb,3] float32; out [la,lb]
+ * float64 (DEVICE), out[i,j] = mean NN distance A_i -> B_j plus mean NN distance B_j -> A_i. */
+int cb_chamfer_cross(cb_ctx* ctx, const float* a, int la, int pa, const float* b, int lb, int pb, double* out,
+                     void* stream);
+
 /* Hausdorff-style max of NN distances (evaluation-shapenet.py:122-155 chamfer_max), same
  * arguments as cb_chamfer one-direction; out [1] float64. */
 int cb_nn_max(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,

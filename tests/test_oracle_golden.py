@@ -147,3 +147,13 @@ def test_shapenet_symmetry_label():
         errs = [e for sym in ps.SYM_ORDERS for e in ps.rotation_errors(sym, pc)]
         np.testing.assert_allclose(errs, g["errors"][c], rtol=0, atol=1e-12)
         assert ps.test_symmetry_label(4, pc, 0.05) == bool(g["test_label4_thr005"][c])
+
+
+def test_scan2cad_shape_branch():
+    """oracle/port_scan2cad.py against vectors made with the reference's chamfer_kdtree_1direction and
+    the app's own cdist / argsort / argmin statements (tests/golden/make_scan2cad_golden.py)."""
+    from oracle import port_scan2cad as sc
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "scan2cad.npz"))
+    np.testing.assert_allclose(sc.chamfer_cross_table(g["gt"], g["recon"]), g["table"], rtol=0, atol=1e-12)
+    top, ret = sc.rerank_by_chamfer(g["desc"], g["lib"], g["ctab"], g["best"], int(g["use_best"]))
+    assert np.array_equal(top, g["topN"]) and np.array_equal(ret, g["retrieved"])
