@@ -690,7 +690,8 @@ int cb_ransac_impl(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, cons
             int P = 1;
             if (use_tc) {
                 cb_timed_scope ts(ctx, CB_T_RANSAC_SCORE, 0.0, st);
-                if ((rc = ransac_tc_score_launch(ctx, Apack_w, Bpack, band_w, Tw_w, src4, tgt4, m, h0, w, thr2, state, pc_w, ps_w, st)))
+                if ((rc = ransac_tc_score_launch(ctx, Apack_w, Bpack, band_w, Tw_w, src4, tgt4, m, h0, w, thr2, state, pc_w, ps_w,
+                                                 sums != nullptr, st)))
                     return rc;
             } else {
                 const int groups = cb_div_up(w, 128 * 2 * NP);

@@ -116,8 +116,8 @@ __device__ inline void ransac_tc_write_weights(const double* T12, const double* 
 // features + maxima of the centred correspondences (launch after ransac_pack_kernel)
 int ransac_tc_pack_corr_launch(cb_ctx* ctx, const float4* src4, const float4* tgt4, int m, RansacState* state,
                                __nv_bfloat16* Bpack, cudaStream_t st);
-// scoring of one wave; atomically ADDS every hypothesis' inlier count / sum of squared inlier
-// distances into pc/ps [w] (zeroed by the fit kernel)
+// scoring of one wave; atomically ADDS every hypothesis' inlier count (and, when want_sum, its sum of
+// squared inlier distances) into pc/ps [w] (zeroed by the fit kernel)
 int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_bfloat16* Bpack, const float* band,
                            const double* Tw, const float4* src4, const float4* tgt4, int m, int h0, int w,
-                           double thr2, const RansacState* state, int32_t* pc, double* ps, cudaStream_t st);
+                           double thr2, const RansacState* state, int32_t* pc, double* ps, bool want_sum, cudaStream_t st);

@@ -139,10 +139,10 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
     return d;
 }
 
-constexpr float kNegBig = -1.2676506e30f;  // -2^100: fma.sat(u, kNegBig, 0) = 1 for u < 0, else 0
-
-// what the streaming pass added for a value u: (g, g*u)
-__device__ __forceinline__ float rt_gate(float u) { return fma_sat(u, kNegBig, 0.f); }
+// what the streaming pass added for a value u: its sign bit to the count (one integer instruction,
+// LEA.HI in SASS; a saturating-FMA gate measured at a quarter of the FMA pipe's rate), min(u, 0) to
+// the sum
+__device__ __forceinline__ unsigned rt_sign(float u) { return __float_as_uint(u) >> 31; }
 
 // exact decision for one evaluation; returns the correction (exact - streamed) of count and sum
 __device__ __forceinline__ void rt_exact_delta(const double* __restrict__ Tj, const float4* __restrict__ src4,
@@ -150,9 +150,8 @@ __device__ __forceinline__ void rt_exact_delta(const double* __restrict__ Tj, co
                                                double& dc, double& ds) {
     const double dd = ransac_exact_d2_inl(Tj, src4[col], tgt4[col]);
     const bool in = dd < thr2d;
-    const float g = rt_gate(u);
-    dc = (in ? 1.0 : 0.0) - (double)g;
-    ds = (in ? dd - thr2d : 0.0) - (double)g * (double)u;
+    dc = (in ? 1.0 : 0.0) - (double)rt_sign(u);
+    ds = (in ? dd - thr2d : 0.0) - (double)fminf(u, 0.f);
 }
 
 // the CTA's queue is full: settle one in-band evaluation on the spot
@@ -179,7 +178,7 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
     }
 }
 
-template <bool DUMP, int LDW = 32>
+template <bool DUMP, int LDW, bool WSUM>
 __global__ void __launch_bounds__(kThreads, 1)
 ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
                        const float* __restrict__ band_g, const double* __restrict__ Tw,
@@ -272,39 +271,47 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         const float band = valid ? band_g[j] : -1.f;
         const double* Tj = Tw + (size_t)min(j, w - 1) * 12;
         const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN + half * kColsPerThread;
-        double cnt_d = 0.0, sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
-        f32x2 c2, s2;
+        double sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
+        unsigned cnt_i = 0;
+        f32x2 s2;
         // one 32-column chunk: gate, count, sum, and the in-band test
         auto process = [&](const float (&v)[32], int colc) {
-            float bm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+            float bm0 = INFINITY, bm1 = INFINITY;
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
-                const float g0 = rt_gate(v[e]), g1 = rt_gate(v[e + 1]);
-                const f32x2 g = pk2(g0, g1);
-                c2 = add2(c2, g);
-                s2 = fma2(g, pk2(v[e], v[e + 1]), s2);
-                bm[e >> 3] = fminf(bm[e >> 3], fminf(fabsf(v[e]), fabsf(v[e + 1])));
+                cnt_i += rt_sign(v[e]) + rt_sign(v[e + 1]);
+                // the streamed sum only feeds cb_ransac's optional `sums` output: the fold recomputes the
+                // sum of every hypothesis tied at the top count exactly
+                if (WSUM) s2 = add2(s2, pk2(fminf(v[e], 0.f), fminf(v[e + 1], 0.f)));
+                if (e & 2) bm1 = fminf(bm1, fminf(fabsf(v[e]), fabsf(v[e + 1])));
+                else bm0 = fminf(bm0, fminf(fabsf(v[e]), fabsf(v[e + 1])));
             }
             if (DUMP) {
                 if (valid)
                     for (int e = 0; e < 32; ++e)
                         if (colc + e < m) dump[(size_t)j * dump_ld + colc + e] = v[e];
             }
-            if (fminf(fminf(bm[0], bm[1]), fminf(bm[2], bm[3])) <= band) {
+            // rare (about one lane-chunk in 500): some evaluation sits inside the rounding band.  Only
+            // the lanes concerned run this: a 32-bit mask of their in-band columns, ONE reservation of
+            // queue slots, then the entries.
+            if (fminf(bm0, bm1) <= band) {
+                // the opaque copy keeps the 32 comparisons inside the branch (the compiler otherwise
+                // hoists them into the streaming loop: 64 more instructions per 32 columns)
+                float band_in;
+                asm volatile("mov.f32 %0, %1;" : "=f"(band_in) : "f"(band));
+                unsigned mask = 0;
 #pragma unroll
-                for (int g8 = 0; g8 < 4; ++g8) {
-                    if (bm[g8] <= band) {
+                for (int e = 0; e < 32; ++e) mask |= (fabsf(v[e]) <= band_in ? 1u : 0u) << e;
+                int pos = atomicAdd(&ctl->list_n, __popc(mask));
+                while (mask) {
+                    const int e = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    float u = 0.f;  // v[e] by static selects: a runtime index would put v in local memory
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const float u = v[g8 * 8 + e];
-                            if (fabsf(u) <= band) {
-                                const int col = colc + g8 * 8 + e;
-                                const int pos = atomicAdd(&ctl->list_n, 1);
-                                if (pos < kListCap) list[pos] = make_int2((rloc << 24) | col, __float_as_int(u));
-                                else rt_overflow(col, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
-                            }
-                        }
-                    }
+                    for (int t = 0; t < 32; ++t) u = t == e ? v[t] : u;
+                    if (pos < kListCap) list[pos] = make_int2((rloc << 24) | (colc + e), __float_as_int(u));
+                    else rt_overflow(colc + e, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
+                    ++pos;
                 }
             }
         };
@@ -314,7 +321,6 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             tc::fence_after_sync();
             const int col0 = (t0 + it) * kRtTileN + half * kColsPerThread;
             const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
-            c2 = pk2(0.f, 0.f);
             s2 = pk2(0.f, 0.f);
             // drain this thread's columns, 64 (or 32) at a time (measured: neither double-buffering the
             // loads nor 16 epilogue warps beats this; the tensor-memory read rate is the limit)
@@ -340,11 +346,11 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             tc::fence_before_sync();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
-            float x, y;
-            unpk2(c2, x, y);
-            cnt_d += (double)x + (double)y;
-            unpk2(s2, x, y);
-            sum_d += (double)x + (double)y;
+            if (WSUM) {
+                float x, y;
+                unpk2(s2, x, y);
+                sum_d += (double)x + (double)y;
+            }
             // every 16 tiles: if the queue is half full (a CTA-uniform decision) drain it
             if ((it & 15) != 15) continue;
             named_bar_sync(1, kEpiThreads);
@@ -361,12 +367,12 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         named_bar_sync(1, kEpiThreads);
         if (valid) {
             // this thread's share of the row; the queue's corrections ride with the first half
-            const double c = cnt_d + dcnt + (half == 0 ? s_dcnt[rloc] : 0.0);
+            const double c = (double)cnt_i + dcnt + (half == 0 ? s_dcnt[rloc] : 0.0);
             const long long ci = llrint(c);
             // totals over column halves and correspondence splits (zeroed by the fit kernel)
             atomicAdd(&pc[j], (int)ci);
             // sum of squared inlier distances = sum (d^2 - thr^2) + count * thr^2
-            atomicAdd(&ps[j], sum_d + dsum + (half == 0 ? s_dsum[rloc] : 0.0) + (double)ci * thr2d);
+            if (WSUM) atomicAdd(&ps[j], sum_d + dsum + (half == 0 ? s_dsum[rloc] : 0.0) + (double)ci * thr2d);
         }
     }
     tc::fence_before_sync();
@@ -410,28 +416,22 @@ int ransac_tc_pack_corr_launch(cb_ctx* ctx, const float4* src4, const float4* tg
 
 int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_bfloat16* Bpack, const float* band,
                            const double* Tw, const float4* src4, const float4* tgt4, int m, int h0, int w,
-                           double thr2, const RansacState* state, int32_t* pc, double* ps, cudaStream_t st) {
+                           double thr2, const RansacState* state, int32_t* pc, double* ps, bool want_sum, cudaStream_t st) {
     if (m >= (1 << 24)) CB_FAIL(ctx, CB_EUNSUPPORTED, "tensor-core RANSAC scoring holds at most 2^24 correspondences");
     int P, tps;
     rt_split_plan(ctx, m, w, &P, &tps);
     float* dump = ctx->ransac_dump;
     const int dump_ld = ctx->ransac_dump_ld;
     cudaError_t e;
-    if (dump) {
-        e = cudaFuncSetAttribute(ransac_tc_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
-        if (e == cudaSuccess)
-            ransac_tc_score_kernel<true><<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
-                Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps,
-                dump + (size_t)h0 * dump_ld, dump_ld);
-    } else {
-        // 64-column tcgen05.ld: 650 vs 664 us per 100 000 x 16 345 registration (CB_RT_LD64=0: 32 columns)
-        static const bool ld64 = !(getenv("CB_RT_LD64") && !atoi(getenv("CB_RT_LD64")));
-        auto kern = ld64 ? ransac_tc_score_kernel<false, 64> : ransac_tc_score_kernel<false, 32>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
-        if (e == cudaSuccess)
-            kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
-                Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps, nullptr, 0);
-    }
+    // 64-column tcgen05.ld: 650 vs 664 us per 100 000 x 16 345 registration; the sum is streamed only
+    // when the caller asked for cb_ransac's per-hypothesis `sums`
+    auto kern = dump ? ransac_tc_score_kernel<true, 32, true>
+                     : (want_sum ? ransac_tc_score_kernel<false, 64, true> : ransac_tc_score_kernel<false, 64, false>);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
+    if (e == cudaSuccess)
+        kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
+            Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps,
+            dump ? dump + (size_t)h0 * dump_ld : nullptr, dump_ld);
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "ransac_tc_score_kernel: %s", cudaGetErrorString(e));
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;
