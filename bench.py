@@ -269,11 +269,14 @@ def run_ours(args, rank, world, local_rank):
         roof = {"bound": "hbm", "kernel": "ransac_tc_score_kernel (" + ctx.ransac_variant() + ")",
                 "achieved": work_k / (ms_k * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
                 "note": f"effective streamed bytes (hypotheses scored x M x 32 B, BASELINE.json's definition); peak = {src} "
-                        "HBM copy bandwidth.  The correspondences live in L2/shared memory, so frac > 1; the kernel's real "
-                        "limiter is draining the GEMM accumulators out of tensor memory (64 B/clk/SM = 16 evaluations/clk/SM): "
-                        "see evals_per_s and tmem_drain_frac",
-                "evals_per_s": work_k / 32.0 / (ms_k * 1e-3),
-                "tmem_drain_frac": (work_k / 32.0 / (ms_k * 1e-3)) / (16.0 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6)}
+                        "HBM copy bandwidth.  The correspondences live in L2/shared memory, so frac > 1; the kernel is "
+                        "a split-bf16 GEMM (K = 96) whose accumulators are drained by tcgen05.ld beside the next tile's "
+                        "MMAs: evals_per_clk_per_sm against the tensor pipe's 42.7 (12 MMAs x 64 clk per 32768 "
+                        "evaluations) is tensor_frac; with its arithmetic compiled out the kernel still needs 70 % of "
+                        "its time (profiles/r01_tmem_ld_microbench.txt)",
+                "evals_per_s": work_k / 32.0 / (ms_k * 1e-3)}
+        roof["evals_per_clk_per_sm"] = roof["evals_per_s"] / (148 * (clocks.get("sm_mhz") or 1965.0) * 1e6)
+        roof["tensor_frac"] = roof["evals_per_clk_per_sm"] / (128.0 * 128.0 * 2 / (12 * 64.0))
     else:
         roof = {"bound": "tensor", "kernel": "knn candidates (" + ctx.knn_variant() + ")",
                 "achieved": work_k / (ms_k * 1e-3) / 1e12, "peak": bf16 / 3.0, "unit": "TFLOP/s",
@@ -306,7 +309,8 @@ def run_ours(args, rank, world, local_rank):
                   "peak": bf16 / 3.0, "frac": knn_tf / (bf16 / 3.0), "us_per_call": ke0.elapsed_time(ke1) / 10 * 1e3,
                   "note": "whole cb_knn call (norms, packing, two-pass tcgen05 candidate kernel, exact re-rank), 2*N0*N1*D "
                           f"flop; peak = {src} sustained bf16 dense / 3 products.  Every score is read out of tensor "
-                          "memory twice (64 B/clk/SM), which caps this at 32 % of that peak (DESIGN.md K1)"}
+                          "memory twice, beside the MMAs' accumulator traffic (measured 88-125 B/clk/SM), which caps this "
+                          "near 22-31 % of that peak (DESIGN.md K1)"}
     del fa, fb
 
     cpu_base = None

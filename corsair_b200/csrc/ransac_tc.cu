@@ -16,8 +16,10 @@
 //   warp 8  producer: cp.async.bulk of the pre-packed A tiles and of a 3-stage ring of B tiles
 //   warp 9  one elected thread issues tcgen05.mma (M=128, N=128, K=16; 6 per tile and A tile) into
 //           a double-buffered TMEM accumulator (2 stages x 2 A tiles x 128 columns = 512)
-//   warps 0-7 epilogue: warp w reads lane quadrant w%4 of A tile w/4 in 32-column tcgen05.ld.
-//           The kernel is bound by this drain: tensor memory reads at 64 B/clk/SM = 16 evaluations/clk/SM
+//   warps 0-7 epilogue: warp w reads lane quadrant w%4 of A tile w/4 in 64-column tcgen05.ld.
+//           Measured (profiles/r01_tmem_ld_microbench.txt): with the arithmetic compiled out the kernel
+//           still needs 70 % of its time — the drain runs at ~88 B/clk/SM beside the MMAs' accumulator
+//           traffic (267+ B/clk/SM on an idle SM) — so the epilogue is kept to 1.5 instructions per value
 #include "ransac_internal.cuh"
 
 #include <stdlib.h>
@@ -323,7 +325,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
             s2 = pk2(0.f, 0.f);
             // drain this thread's columns, 64 (or 32) at a time (measured: neither double-buffering the
-            // loads nor 16 epilogue warps beats this; the tensor-memory read rate is the limit)
+            // loads nor 16 epilogue warps changes the time)
             if constexpr (LDW == 64) {
 #pragma unroll 1
                 for (int k = 0; k < kChunks; k += 2) {
