@@ -229,10 +229,13 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                         }
                     }
                 } else {
-                    // which of the 32 columns qualify: a bit mask (branch-free)
-                    unsigned mask = 0;
+                    // which of the 32 columns qualify: a bit mask, two instructions per column on two
+                    // pipes — the sign bit of v - tau (set: below the threshold) is shifted into the word
+                    // by one funnel shift; column e lands at bit 31 - e, hence the bit reversal
+                    unsigned below = 0;
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) mask |= (v[e] >= tau ? 1u : 0u) << e;
+                    for (int e = 0; e < 32; ++e) below = __funnelshift_l(__float_as_uint(v[e] - tau), below, 1);
+                    unsigned mask = __brev(~below);
                     // padding rows (all-equal scores) and rows whose list already overflowed (they go
                     // to the exact fallback whatever else qualifies) must not spin in the loop below
                     if (!live || (mask && *(volatile int*)&s_cnt[row] > LC)) mask = 0;
