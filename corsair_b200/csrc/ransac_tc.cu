@@ -145,6 +145,14 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 // LEA.HI in SASS; a saturating-FMA gate measured at a quarter of the FMA pipe's rate), min(u, 0) to
 // the sum
 __device__ __forceinline__ unsigned rt_sign(float u) { return __float_as_uint(u) >> 31; }
+// ... for half of the columns; the other half is counted on the FMA pipe (fma.sat gate + packed add)
+// so that both pipes share the epilogue: column c takes the float path when bit 1 of c is clear
+constexpr float kNegBig = -1.2676506e30f;  // -2^100: fma.sat(u, kNegBig, 0) = 1 for u < 0, else 0
+__device__ __forceinline__ float rt_gate(float u) { return fma_sat(u, kNegBig, 0.f); }
+__device__ __forceinline__ bool rt_float_path(int col) { return (col & 2) == 0; }
+__device__ __forceinline__ double rt_streamed_count(int col, float u) {
+    return rt_float_path(col) ? (double)rt_gate(u) : (double)rt_sign(u);
+}
 
 // exact decision for one evaluation; returns the correction (exact - streamed) of count and sum
 __device__ __forceinline__ void rt_exact_delta(const double* __restrict__ Tj, const float4* __restrict__ src4,
@@ -152,7 +160,7 @@ __device__ __forceinline__ void rt_exact_delta(const double* __restrict__ Tj, co
                                                double& dc, double& ds) {
     const double dd = ransac_exact_d2_inl(Tj, src4[col], tgt4[col]);
     const bool in = dd < thr2d;
-    dc = (in ? 1.0 : 0.0) - (double)rt_sign(u);
+    dc = (in ? 1.0 : 0.0) - rt_streamed_count(col, u);
     ds = (in ? dd - thr2d : 0.0) - (double)fminf(u, 0.f);
 }
 
@@ -275,13 +283,14 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + a * kRtTileN + half * kColsPerThread;
         double sum_d = 0.0, dcnt = 0.0, dsum = 0.0;
         unsigned cnt_i = 0;
-        f32x2 s2;
+        f32x2 s2, c2;
         // one 32-column chunk: gate, count, sum, and the in-band test
         auto process = [&](const float (&v)[32], int colc) {
             float bm0 = INFINITY, bm1 = INFINITY;
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
-                cnt_i += rt_sign(v[e]) + rt_sign(v[e + 1]);
+                if (e & 2) cnt_i += rt_sign(v[e]) + rt_sign(v[e + 1]);
+                else c2 = add2(c2, pk2(rt_gate(v[e]), rt_gate(v[e + 1])));
                 // the streamed sum only feeds cb_ransac's optional `sums` output: the fold recomputes the
                 // sum of every hypothesis tied at the top count exactly
                 if (WSUM) s2 = add2(s2, pk2(fminf(v[e], 0.f), fminf(v[e + 1], 0.f)));
@@ -324,6 +333,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             const int col0 = (t0 + it) * kRtTileN + half * kColsPerThread;
             const uint32_t taddr = lane_addr + ts * (kHT * kRtTileN);
             s2 = pk2(0.f, 0.f);
+            c2 = pk2(0.f, 0.f);
             // drain this thread's columns, 64 (or 32) at a time (measured: neither double-buffering the
             // loads nor 16 epilogue warps changes the time)
             if constexpr (LDW == 64) {
@@ -348,10 +358,14 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             tc::fence_before_sync();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
-            if (WSUM) {
+            {
                 float x, y;
-                unpk2(s2, x, y);
-                sum_d += (double)x + (double)y;
+                unpk2(c2, x, y);  // at most 64 per tile: exact in fp32
+                cnt_i += (unsigned)(x + y);
+                if (WSUM) {
+                    unpk2(s2, x, y);
+                    sum_d += (double)x + (double)y;
+                }
             }
             // every 16 tiles: if the queue is half full (a CTA-uniform decision) drain it
             if ((it & 15) != 15) continue;
