@@ -593,7 +593,14 @@ __global__ void ransac_expand_T_kernel(const double* __restrict__ Tw, int h, dou
 
 // Waves of hypotheses: a small first wave (most adaptive runs stop inside it), then waves that give
 // every SM one 256-hypothesis CTA of the tensor-core scoring kernel.
-constexpr int kWaveFirst = 4096;
+static int ransac_wave_first() {
+    static const int v = [] {
+        const char* e = getenv("CB_RANSAC_WAVE_FIRST");  // tuning knob: hypotheses in the first wave
+        int x = e ? atoi(e) : 4096;
+        return x < 256 ? 256 : (x > 40960 ? 40960 : x / 256 * 256);
+    }();
+    return v;
+}
 static int ransac_wave_max(const cb_ctx* ctx) {
     static int override_ctas = -1;  // CB_RANSAC_WAVE_CTAS: tuning knob (CTAs of 256 hypotheses per wave)
     if (override_ctas < 0) {
@@ -601,10 +608,10 @@ static int ransac_wave_max(const cb_ctx* ctx) {
         override_ctas = e ? atoi(e) : 0;
     }
     const int ctas = override_ctas > 0 ? min(override_ctas, 160) : min(ctx->sm_count, 160);
-    return max(kWaveFirst, ctas * 256);
+    return max(ransac_wave_first(), ctas * 256);
 }
 static int ransac_wave_size(const cb_ctx* ctx, int wave_index) {
-    return wave_index == 0 ? kWaveFirst : ransac_wave_max(ctx);
+    return wave_index == 0 ? ransac_wave_first() : ransac_wave_max(ctx);
 }
 
 // workspace cb_ransac_impl needs (an upper bound, both scoring variants)
@@ -633,7 +640,7 @@ int cb_ransac_impl(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, cons
     const int m_pad = cb_div_up(max(m, 1), kRtTileN) * kRtTileN;
     // tensor-core path: after the first wave ONE fit launch covers every remaining hypothesis (it
     // fills the machine better than a fit per wave), so the per-hypothesis buffers span the whole run
-    const bool merged = use_tc && h_total > kWaveFirst && h_total <= (1 << 18);
+    const bool merged = use_tc && h_total > ransac_wave_first() && h_total <= (1 << 18);
     const size_t hcap = merged ? (size_t)h_total : (size_t)wmax;
     const size_t n_tot = use_tc ? hcap : pw_max;
     size_t need = cb_align(sizeof(RansacState)) + 2 * cb_align((size_t)(m + 1) * 16) +
