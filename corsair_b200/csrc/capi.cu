@@ -50,6 +50,7 @@ extern "C" int cb_destroy(cb_ctx* ctx) {
     for (auto s : ctx->sub_stream) cudaStreamDestroy(s);
     for (auto c : ctx->sub) cb_destroy(c);
     if (ctx->fork_event) cudaEventDestroy(ctx->fork_event);
+    if (ctx->sync_event) cudaEventDestroy(ctx->sync_event);
     for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;

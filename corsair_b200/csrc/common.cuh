@@ -38,6 +38,7 @@ struct cb_ctx {
     std::vector<cudaStream_t> sub_stream;
     std::vector<cudaEvent_t> sub_event;
     cudaEvent_t fork_event = nullptr;
+    cudaEvent_t sync_event = nullptr;  // blocking-sync event: the host thread sleeps instead of spinning
 };
 
 // Bracket one tracked launch with events when timing is on.
