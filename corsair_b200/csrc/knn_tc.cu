@@ -209,11 +209,8 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             tc::mbar_wait(&ctl->tmem_full[st], use & 1);
             tc::fence_after_sync();
             const int col0 = (t0 + (second ? it - ntiles : it)) * kTileN + half * kHalfN;
-#pragma unroll 1
-            for (int cb = 0; cb < kHalfN / 32; ++cb) {
-                float v[32];
-                tc::tmem_ld32(lane_addr + st * kTileN + cb * 32, v);
-                tc::tmem_ld_wait();
+            // one 32-column chunk of this thread's half of the stage
+            auto process = [&](const float (&v)[32], int cb) {
                 if (!second) {
 #pragma unroll
                     for (int g = 0; g < 32 / GROUP; ++g) {
@@ -249,10 +246,26 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                             cand_idx[o + pos] = (int)(((unsigned long long)(col0 + cb * 32 + e) * perm_inv) % (unsigned)nr_pad);
                     }
                 }
-            }
+            };
+            // software-pipelined drain: the next 32 columns are in flight while these are processed;
+            // the stage goes back to the MMA warp as soon as its last load has landed
+            static_assert(kHalfN / 32 == 4, "four chunks per stage and thread");
+            float va[32], vb[32];
+            tc::tmem_ld32(lane_addr + st * kTileN, va);
+            tc::tmem_ld_wait32(va);
+            tc::tmem_ld32(lane_addr + st * kTileN + 32, vb);
+            process(va, 0);
+            tc::tmem_ld_wait32(vb);
+            tc::tmem_ld32(lane_addr + st * kTileN + 64, va);
+            process(vb, 1);
+            tc::tmem_ld_wait32(va);
+            tc::tmem_ld32(lane_addr + st * kTileN + 96, vb);
+            process(va, 2);
+            tc::tmem_ld_wait32(vb);
             tc::fence_before_sync();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
+            process(vb, 3);
         }
         named_bar_sync(1, kEpiWarps * 32);  // both halves of every row have appended
         if (live && half == 0) {

@@ -110,6 +110,13 @@ __device__ __forceinline__ void tmem_ld_wait64(float* v) {
                  :
                  : "memory");
 }
+__device__ __forceinline__ void tmem_ld_wait32(float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :
+                 : "memory");
+}
 // ---- descriptors ----------------------------------------------------------------------------
 // K-major, SWIZZLE_NONE canonical layout: core matrix = 8 rows x 16 bytes stored contiguously
 // (128 B); SBO = byte distance between core matrices adjacent along M/N (8-row groups), LBO =
