@@ -157,3 +157,37 @@ def test_scan2cad_shape_branch():
     np.testing.assert_allclose(sc.chamfer_cross_table(g["gt"], g["recon"]), g["table"], rtol=0, atol=1e-12)
     top, ret = sc.rerank_by_chamfer(g["desc"], g["lib"], g["ctab"], g["best"], int(g["use_best"]))
     assert np.array_equal(top, g["topN"]) and np.array_equal(ret, g["retrieved"])
+
+
+def test_evaluation_cache_and_metric_tables(tmp_path):
+    """evaluation_registration: the nine cache files (evaluation.py:390-441 names and shapes) round-trip,
+    and the RTE / RRE tables equal the restated closures of :336-348 (and hand-computed values)."""
+    from corsair_b200 import evaluation_registration as er
+    from oracle import port_evaluation as pe
+    rng = np.random.default_rng(3)
+    n = 23
+    res = {
+        "Ts_est_ransac": [rng.standard_normal((4, 4)).astype(np.float32) for _ in range(n)],
+        "Ts_est_best": [rng.standard_normal((4, 4)).astype(np.float32) for _ in range(n)],
+        "t_losses_ransac": list(rng.random(n) * 0.2), "t_losses_sym": list(rng.random(n) * 0.1),
+        "r_losses_ransac": list(rng.random(n) * 1.0), "r_losses_sym": list(rng.random(n) * 0.3),
+        "sym_ransac_success": [bool(b) for b in rng.random(n) < 0.8],
+        "chamfer_dist_ransac": list(rng.random(n) * 0.05), "chamfer_dist_sym": list(rng.random(n) * 0.04),
+    }
+    assert er.load_results(str(tmp_path), "chair", True) is None
+    er.save_results(str(tmp_path), "chair", True, res)
+    assert sorted(os.listdir(tmp_path)) == sorted(f"{k}_chair_top1.npy" for k in er.KEYS)
+    assert np.load(tmp_path / "Ts_est_best_chair_top1.npy").shape == (n, 16)
+    assert er.load_results(str(tmp_path), "chair", False) is None  # the _gt files are a different cache
+    back = er.load_results(str(tmp_path), "chair", True)
+    for k in er.KEYS:
+        assert np.array_equal(np.asarray(back[k]), np.asarray(res[k])), k
+    assert back["Ts_est_ransac"][0].shape == (4, 4)
+    s, text = er.summarize(back)
+    assert (s["rte_002_ransac"], s["rte_005_ransac"], s["rte_010_ransac"], s["rte_015_ransac"]) == pe.compute_rte(res["t_losses_ransac"])
+    assert (s["rre_005_sym"], s["rre_015_sym"], s["rre_045_sym"]) == pe.compute_rre(res["r_losses_sym"])
+    assert s["sym_success_rate"] == np.mean(res["sym_ransac_success"]) and s["t_loss_sym"] == np.mean(res["t_losses_sym"])
+    assert "vanilla ransac:" in text and "sym ransac:" in text and f"sym success rate: {s['sym_success_rate']}" in text
+    # hand-computed: thresholds are inclusive
+    assert pe.compute_rte([0.02, 0.05, 0.2, 0.01]) == (0.5, 0.75, 0.75, 0.75)
+    assert pe.compute_rre(np.deg2rad([4.0, 20.0, 50.0, 10.0])) == (0.25, 0.5, 0.75)
