@@ -70,6 +70,7 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_u64,
                                      c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cb_np_seeded_choices": (c_int, [ctypes.c_uint32, c_void_p, c_int, c_int, c_void_p]),  # no context argument
+    "cb_voxel_unique": (c_int, [c_void_p, c_void_p, c_int, ctypes.c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cb_sym_pose": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                             c_void_p, c_void_p, c_int, ctypes.c_int64, c_int, c_void_p, c_void_p, c_int, c_int,
                             c_double, c_double, c_u64, c_int, c_int, c_double, c_void_p, c_void_p]),

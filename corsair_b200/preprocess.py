@@ -67,3 +67,35 @@ def chamfer_kdtree_1direction(pc0, pc1):
     float64 inputs (e.g. the output of apply_transform) are rounded to float32 for the search;
     use ``chamfer_device(xyz, pc1, T)`` to apply a pose in float64 on the device instead."""
     return float(_chamfer(pc0, pc1, None, False).item())
+
+
+def quantize_pc(pc, voxel_size):
+    """evaluation-shapenet.py:97-107 (and the library-side dedup of utils/Info/CADLib.py:106-121) on
+    the device: one point per occupied voxel -> (pc [M,3] float32, pc_grid [M,3] int32) as tensors on
+    the input's device (CUDA for NumPy input).  Kept point = the first (lowest index) of its voxel,
+    output in ascending index order: ``np.unique(np.floor(pc / v), axis=0, return_index=True)`` with
+    the indices sorted.  MinkowskiEngine's own choice among duplicates cannot be checked here (not
+    installed): DESIGN.md lists this call as parity-unpinned."""
+    ctx = _capi.get_context()
+    p = ctx.dev(pc, torch.float32)
+    n = p.shape[0]
+    idx = ctx.empty((max(n, 1),), torch.int64)
+    grid = ctx.empty((max(n, 1), 3), torch.int32)
+    count = ctx.empty((1,), torch.int32)
+    ctx.call("cb_voxel_unique", ptr(p), n, float(voxel_size), ptr(idx), ptr(grid), ptr(count), ctx.stream)
+    m = int(count.item())
+    if m < 0:
+        raise ValueError("quantize_pc: a coordinate is not finite or beyond 2^20 voxels")
+    return p[idx[:m]], grid[:m]
+
+
+def split_batch(C, F):
+    """model/fc.py:23-29 for the tensors of a sparse output (``sp.C`` [N,1+3] int, ``sp.F`` [N,D]):
+    the feature rows of every batch index, in their original order, as a list of device tensors —
+    the hand-off from the feature producer to sym_pose without a ``.cpu().numpy()`` round trip.
+    One stable sort + one bincount (a single host read of the counts) instead of one boolean mask,
+    and one synchronisation, per batch item."""
+    b = C[:, 0].long()
+    counts = torch.bincount(b)
+    order = torch.argsort(b, stable=True)
+    return list(F[order].split(counts.tolist()))

@@ -261,6 +261,14 @@ int cb_register_pairings(cb_ctx* ctx, const float* base_f, const float* base_xyz
  * (NumPy raises there). */
 int cb_np_seeded_choices(uint32_t seed, const int32_t* n, int count, int size, int32_t* out);
 
+/* Voxel de-duplication (quantize_pc, evaluation-shapenet.py:97-107; utils/Info/CADLib.py:106-121): for
+ * xyz [n,3] float32 the indices of the points that are the FIRST (lowest index) in their voxel
+ * floor(p / voxel), ascending: idx_out [<= n] int64, their integer voxel coordinates grid_out
+ * [<= n, 3] int32 (may be NULL), and *count (DEVICE int32) = how many (-1: a coordinate beyond
+ * +-2^20 voxels or not finite).  float32 division and floor, like NumPy on float32 input. */
+int cb_voxel_unique(cb_ctx* ctx, const float* xyz, int n, float voxel, int64_t* idx_out, int32_t* grid_out,
+                    int32_t* count, void* stream);
+
 /* ---- sym_pose end to end (utils/symmetry.py:262-358) ------------------------------------------
  * One call per query-CAD pair: the vanilla registration, the symmetry segmentation of both clouds
  * (symmetric_cut4 with K = 4 when pos_sym >= 2, else 2: :289-298) and, when both accept a model,

@@ -81,3 +81,45 @@ def test_registration_worker_and_register_many(ctx):
                 assert torch.equal(a[k], b[k])
             else:
                 assert a[k] == b[k] or (np.isnan(a[k]) and np.isnan(b[k]))
+
+
+@pytest.mark.parametrize("n,voxel", [(1, 0.03), (257, 0.03), (10000, 0.03), (50000, 0.01), (4000, 0.5)])
+def test_quantize_pc_vs_oracle(ctx, rng, n, voxel):
+    """cb_voxel_unique: first point of every occupied voxel, ascending (numpy.unique rule)."""
+    from corsair_b200 import preprocess
+    pc = (rng.standard_normal((n, 3)) * 0.4).astype(np.float32)
+    if n > 100:
+        pc[n // 2:n // 2 + 50] = pc[:50]          # exact duplicates
+        pc[-10:] = -np.abs(pc[-10:]) - 0.3         # negative voxels
+    ref_pc, ref_grid, _ = ps.quantize_pc(pc, np.float32(voxel))
+    got_pc, got_grid = preprocess.quantize_pc(pc, voxel)
+    assert got_pc.dtype == torch.float32 and got_grid.dtype == torch.int32 and got_pc.is_cuda
+    assert np.array_equal(got_pc.cpu().numpy(), ref_pc) and np.array_equal(got_grid.cpu().numpy(), ref_grid)
+    # CUDA input stays where it is; the synthetic generator's dedup is the same rule
+    again, _ = preprocess.quantize_pc(torch.from_numpy(pc).cuda(), voxel)
+    assert torch.equal(again, got_pc)
+    assert np.array_equal(synth.voxel_dedup(pc, voxel), ref_pc)
+
+
+def test_quantize_pc_edge_cases(ctx):
+    from corsair_b200 import preprocess
+    e_pc, e_grid = preprocess.quantize_pc(np.zeros((0, 3), np.float32), 0.03)
+    assert e_pc.shape == (0, 3) and e_grid.shape == (0, 3)
+    same = np.tile(np.array([[0.011, -0.02, 0.5]], np.float32), (300, 1))
+    p, g = preprocess.quantize_pc(same, 0.03)
+    assert p.shape == (1, 3) and g.cpu().tolist() == [[0, -1, 16]]
+    with pytest.raises(ValueError):
+        preprocess.quantize_pc(np.array([[0.0, np.inf, 0.0]], np.float32), 0.03)
+    with pytest.raises(ValueError):
+        preprocess.quantize_pc(np.array([[1e9, 0.0, 0.0]], np.float32), 0.03)
+
+
+def test_split_batch_matches_mask_loop(ctx, rng):
+    from corsair_b200 import preprocess
+    b = torch.from_numpy(rng.integers(0, 5, 3000)).int()
+    b[b == 3] = 4                                  # an empty batch index in the middle
+    C = torch.cat([b[:, None], torch.zeros((3000, 3), dtype=torch.int32)], 1).cuda()
+    F = torch.from_numpy(rng.standard_normal((3000, 16)).astype(np.float32)).cuda()
+    got = preprocess.split_batch(C, F)
+    ref = [F[C[:, 0] == i, :] for i in range(1 + int(C[:, 0].max()))]   # model/fc.py:23-29
+    assert len(got) == len(ref) and all(torch.equal(a, r) for a, r in zip(got, ref))
