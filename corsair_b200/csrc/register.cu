@@ -274,7 +274,9 @@ extern "C" int cb_sym_pose(cb_ctx* ctx, const float* base_f, const float* base_x
         cb_ctx* c = ctx->sub[j];
         c->knn_variant = ctx->knn_variant;
         c->ransac_variant = ctx->ransac_variant;
-        if ((rc = cb_begin(c)) || (rc = cb_reserve(c, reg_one_workspace(c, a) + (1 << 20)))) {
+        size_t sub_need = reg_one_workspace(c, a);
+        if (j == 1 && scratch > sub_need) sub_need = scratch;  // sub-context 1 also runs the pos segmentation
+        if ((rc = cb_begin(c)) || (rc = cb_reserve(c, sub_need + (1 << 20)))) {
             snprintf(ctx->err, sizeof(ctx->err), "%s", c->err);
             return rc;
         }
@@ -333,14 +335,40 @@ extern "C" int cb_sym_pose(cb_ctx* ctx, const float* base_f, const float* base_x
         const int32_t* d_first = d_s + 2 * n_samples;
         const double* d_unif = reinterpret_cast<const double*>(d_in + cb_align((size_t)2 * n_samples * 4 + (size_t)n_init * 4));
         const size_t mark = ctx->arena_off;
-        rc = cb_segment_impl(ctx, base_f, base_xyz, n0, d, K, d_s, n_samples, n_nn < n0 ? n_nn : n0, d_first, d_unif,
-                             n_init, n_trials, min_center, a_perm, d_off, st);
-        ctx->arena_off = mark;
-        if (rc) return bail(rc);
-        rc = cb_segment_impl(ctx, pos_f, pos_xyz, n1, d, K, d_s + n_samples, n_samples, n_nn < n1 ? n_nn : n1, d_first,
-                             d_unif, n_init, n_trials, min_center, b_perm, d_off + 8, st);
-        ctx->arena_off = mark;
-        if (rc) return bail(rc);
+        // the pos cloud's segmentation is independent of the base cloud's: second internal stream
+        if (n_sub >= 2) {
+            cb_ctx* c = ctx->sub[1];
+            cudaStream_t s = ctx->sub_stream[1];
+            if (cudaEventRecord(ctx->fork_event, st) != cudaSuccess ||
+                cudaStreamWaitEvent(s, ctx->fork_event, 0) != cudaSuccess)
+                return bail(CB_ECUDA);
+            forked = true;
+            used |= 2u;
+            const size_t m1 = c->arena_off;
+            rc = cb_segment_impl(c, pos_f, pos_xyz, n1, d, K, d_s + n_samples, n_samples, n_nn < n1 ? n_nn : n1, d_first,
+                                 d_unif, n_init, n_trials, min_center, b_perm, d_off + 8, s);
+            c->arena_off = m1;
+            if (rc) {
+                snprintf(ctx->err, sizeof(ctx->err), "%s", c->err);
+                return bail(rc);
+            }
+            rc = cb_segment_impl(ctx, base_f, base_xyz, n0, d, K, d_s, n_samples, n_nn < n0 ? n_nn : n0, d_first, d_unif,
+                                 n_init, n_trials, min_center, a_perm, d_off, st);
+            ctx->arena_off = mark;
+            if (rc) return bail(rc);
+            if (cudaEventRecord(ctx->sub_event[1], s) != cudaSuccess ||
+                cudaStreamWaitEvent(st, ctx->sub_event[1], 0) != cudaSuccess)
+                return bail(CB_ECUDA);
+        } else {
+            rc = cb_segment_impl(ctx, base_f, base_xyz, n0, d, K, d_s, n_samples, n_nn < n0 ? n_nn : n0, d_first, d_unif,
+                                 n_init, n_trials, min_center, a_perm, d_off, st);
+            ctx->arena_off = mark;
+            if (rc) return bail(rc);
+            rc = cb_segment_impl(ctx, pos_f, pos_xyz, n1, d, K, d_s + n_samples, n_samples, n_nn < n1 ? n_nn : n1,
+                                 d_first, d_unif, n_init, n_trials, min_center, b_perm, d_off + 8, st);
+            ctx->arena_off = mark;
+            if (rc) return bail(rc);
+        }
         if (cudaMemcpyAsync(pin_off, d_off, 16 * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
             sym_wait(ctx, st) != cudaSuccess) {
             snprintf(ctx->err, sizeof(ctx->err), "cb_sym_pose: segment offsets: %s", cudaGetErrorString(cudaGetLastError()));
