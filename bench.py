@@ -1,22 +1,29 @@
 #!/usr/bin/env python
 """Benchmark of the correspondence-and-registration hot path (BASELINE.json metric: query-CAD
-pairs registered per second).
+pairs registered per second at 1/2/4/8 B200; kNN % of tensor peak).
 
-One step = one query of BASELINE.json configs[1]: a 256-d global descriptor is ranked against a
-synthetic ShapeNet-chair-sized library (6778 CADs), and the query scan is registered against each
-of the top-10 candidates with the full symmetry-aided pipeline (sym_pose: feature 5-NN ->
-correspondence RANSAC (budget 100000, Open3D's adaptive stop) -> Chamfer, two symmetry
-segmentations, K more {per-segment kNN, RANSAC, Chamfer} pairings).  So a step registers 10 pairs.
+Headline workload = BASELINE.json configs[2] ("C3", the full chair evaluation sweep of
+evaluation.py:297-313): every rank registers its share of synthetic Scan2CAD-style chair queries
+against their top-10 retrieved CADs.  One step = QUERIES_PER_STEP queries of this rank: their 256-d
+descriptors are ranked against the 6778-CAD library in one batch, then every (query, candidate) pair
+goes through the full symmetry-aided pipeline (sym_pose: feature 5-NN -> correspondence RANSAC
+(budget 100000, Open3D's adaptive stop) -> Chamfer, two symmetry segmentations, K more {per-segment
+kNN, RANSAC, Chamfer} pairings).  So a step registers QUERIES_PER_STEP x 10 = 100 pairs per rank and
+the driver's 20 steps are a 2000-pair sweep per rank (weak scaling: the per-rank sweep is fixed).
 
-  value  device-resident inputs (query + CAD library already in HBM), timed with CUDA events
-  e2e    the same step through the reference-facing Python API with HOST NumPy buffers
-         (host->device copies and the device->host result reads inside the timed region)
-Both register a step's 10 independent pairs through symmetry.sym_pose_many on WORKERS host threads
-(own cb_ctx + CUDA stream each), like the reference's thread_map loops; the roofline / kernel-class
-numbers come from a separate instrumented pass that runs the pairs one after the other.
+  value  device-resident inputs (queries + CAD library already in HBM), timed with CUDA events
+  e2e    the same steps through the reference-facing Python API with HOST NumPy buffers
+         (host->device copies and the device->host result reads inside the timed region; the bytes
+         are counted where the copies are made)
+Sub-objects on the same line: `d16` (the same sweep at the feature width the shipped scripts use,
+evaluation.py:183), `c5` (table category, 50k-point scans, 4096 hypotheses, nine registrations per
+pair), `c4` (all-pairs Chamfer table 6778 x 2048 points, rows sharded over the ranks), `sharded`
+(the three exchanges of SURVEY.md 8(e) run over the ranks and checked bit for bit against the
+single-GPU result), `knn_tensor` (the metric's second half), `roofline`, `cpu_baseline`.
 
 `python bench.py --impl reference` times the CPU path instead (the oracle's restatement of the
-reference's algorithm on all host cores), one pair per step as a bounded sample.
+reference's algorithm on all host cores): per step ONE pair drawn uniformly (same seed) from the
+step's 100 pairs, as a bounded sample.
 """
 import argparse
 import json
@@ -26,41 +33,79 @@ import sys
 import threading
 import time
 
-import numpy as np
+# the CPU arm must see every host core: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+# silently single-thread the OpenMP restatement of the RANSAC call, sklearn and the BLAS underneath
+if "reference" in sys.argv or int(os.environ.get("WORLD_SIZE", "1")) == 1:
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(os.cpu_count())
+
+import numpy as np  # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-L_DB, D_DESC, TOPK, D_FEAT, CAD_POOL, N_QUERIES = 6778, 256, 10, 32, 32, 8
+L_DB, D_DESC, TOPK, CAD_POOL, QUERIES_PER_STEP = 6778, 256, 10, 48, 10
 K_NN, MAX_CORR, SEED = 5, 0.2, 31
-WORKLOAD = ("C2: 1 query descriptor vs 6778-CAD chair DB, top-10, then sym_pose registration of each "
-            "candidate (10 pairs/step)")
+PAIRS_PER_STEP = QUERIES_PER_STEP * TOPK
+WORKLOAD = ("C3: chair evaluation sweep — per step 10 synthetic Scan2CAD chair queries x top-10 of a 6778-CAD "
+            "library, sym_pose registration of each pair (100 pairs/step/rank)")
+L_TABLE, C4_L, C4_P = 8436, 6778, 2048
+TABLE_SYM_HIST = {1: 233, 2: 422, 3: 7, 4: 128, 12: 40}  # configs/04379243_scan2cad_rot_sym_label.txt
 
 
-def build_workload(rank):
-    """Seeded synthetic inputs (corsair_b200/synth.py): the CAD library holds CAD_POOL distinct
-    procedural chairs (DB row i uses chair i % CAD_POOL); each query is a moved, thinned, jittered
-    copy of its ground-truth CAD with a noisy copy of that row's descriptor."""
-    from corsair_b200 import synth
-    lib, _, _ = synth.descriptor_db(1000, L=L_DB, Q=1, d=D_DESC)
-    pairs = [synth.make_pair(100 + c, D_FEAT, "chair") for c in range(CAD_POOL)]
-    cads = [dict(F=p["posF"], xyz=p["xyz1"], sym=p["pos_sym"]) for p in pairs]
-    rng = np.random.default_rng(7000 + rank)
-    queries = []
-    for i in range(N_QUERIES):
-        g = int(rng.integers(0, L_DB))
-        desc = lib[g] + 0.3 * rng.standard_normal(D_DESC).astype(np.float32) / np.sqrt(D_DESC)
-        desc = (desc / np.linalg.norm(desc)).astype(np.float32)[None]
-        src = pairs[g % CAD_POOL]
-        keep = rng.random(len(src["xyz1"])) > 0.2
-        T = synth.random_pose(rng)
-        xyz0 = ((src["xyz1"][keep] + 0.005 * rng.standard_normal((int(keep.sum()), 3))) @ T[:3, :3].T
-                + T[:3, 3]).astype(np.float32)
-        F0 = src["posF"][keep] + 0.05 * rng.standard_normal((int(keep.sum()), D_FEAT)).astype(np.float32)
-        F0 = (F0 / np.linalg.norm(F0, axis=1, keepdims=True)).astype(np.float32)
-        queries.append(dict(desc=desc, F=F0, xyz=xyz0, gt=g))
-    return lib, cads, queries
+# ------------------------------------------------------------------------------------ workloads
+class Sweep:
+    """Seeded synthetic inputs of the C3 sweep (corsair_b200/synth.py).  The CAD library holds
+    CAD_POOL distinct procedural chairs (DB row i uses chair i % CAD_POOL) whose bulk is drawn so that
+    the de-duplicated clouds span 2.6k-8.0k points; a query is a moved, thinned,
+    jittered copy of its ground-truth CAD with a noisy copy of that row's descriptor."""
+
+    def __init__(self, rank, d_feat, n_steps):
+        from corsair_b200 import synth
+        self.d = d_feat
+        self.lib, _, _ = synth.descriptor_db(1000, L=L_DB, Q=1, d=D_DESC)
+        brng = np.random.default_rng(4242)
+        bulks = np.exp(brng.uniform(np.log(0.5), np.log(10.0), CAD_POOL))
+        pairs = [synth.make_pair(100 + c, d_feat, "chair", bulk=float(bulks[c])) for c in range(CAD_POOL)]
+        self.cads = [dict(F=p["posF"], xyz=p["xyz1"], sym=p["pos_sym"]) for p in pairs]
+        rng = np.random.default_rng(7000 + rank)
+        self.steps = []
+        for _ in range(n_steps):
+            qs = []
+            for _ in range(QUERIES_PER_STEP):
+                g = int(rng.integers(0, L_DB))
+                desc = self.lib[g] + 0.3 * rng.standard_normal(D_DESC).astype(np.float32) / np.sqrt(D_DESC)
+                desc = (desc / np.linalg.norm(desc)).astype(np.float32)
+                src = pairs[g % CAD_POOL]
+                keep = rng.random(len(src["xyz1"])) > 0.2
+                T = synth.random_pose(rng)
+                xyz0 = ((src["xyz1"][keep] + 0.005 * rng.standard_normal((int(keep.sum()), 3))) @ T[:3, :3].T
+                        + T[:3, 3]).astype(np.float32)
+                F0 = src["posF"][keep] + 0.05 * rng.standard_normal((int(keep.sum()), d_feat)).astype(np.float32)
+                F0 = (F0 / np.linalg.norm(F0, axis=1, keepdims=True)).astype(np.float32)
+                qs.append(dict(desc=desc, F=F0, xyz=xyz0, gt=g))
+            self.steps.append(dict(desc=np.stack([q["desc"] for q in qs]), queries=qs))
+
+    def point_counts(self):
+        n0 = [len(q["xyz"]) for s in self.steps for q in s["queries"]]
+        n1 = [len(c["xyz"]) for c in self.cads]
+        return dict(query_min=int(min(n0)), query_max=int(max(n0)), cad_min=int(min(n1)), cad_max=int(max(n1)))
+
+    def to(self, fn):
+        """Copy of the sweep with every array mapped through fn (device upload / pinning)."""
+        import copy
+        o = copy.copy(self)
+        o.lib = fn(self.lib)
+        o.cads = [dict(F=fn(c["F"]), xyz=fn(c["xyz"]), sym=c["sym"]) for c in self.cads]
+        o.steps = [dict(desc=fn(s["desc"]), queries=[dict(F=fn(q["F"]), xyz=fn(q["xyz"]), gt=q["gt"]) for q in s["queries"]])
+                   for s in self.steps]
+        return o
+
+
+def candidate_pairs(order, step):
+    """(query index, CAD pool index) of a step's pairs, in registration order."""
+    return [(qi, int(c) % CAD_POOL) for qi in range(len(step["queries"])) for c in order[qi]]
 
 
 class ClockSampler:
@@ -89,20 +134,24 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         for r in self.rows:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
+                pw.append(float(r[3]))
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
                     if v.lower().startswith("active"):
                         reasons.add(name)
             except (ValueError, IndexError):
                 pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        # "under load": the samples drawing more than half of the highest power seen
+        load = [s for s, p in zip(sm, pw) if pw and p >= 0.5 * max(pw)] or sm
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+# ------------------------------------------------------------------------------------ CPU arm
 def cpu_pair(q, cad):
     """One registered pair on the CPU: the oracle's restatement of sym_pose (reference Python
     algorithm: scipy KD-tree kNN with workers=-1, sklearn KMeans segmentation, KD-tree Chamfer)
@@ -118,12 +167,18 @@ def cpu_pair(q, cad):
                                   seed=SEED, registration=reg)
 
 
-def cpu_step(lib, cads, q, n_pairs):
+def cpu_sample(sweep, step_index, rng, n_pairs):
+    """Retrieval of the whole step (cdist + stable argsort, utils/retrieval.py:170-177) and n_pairs of
+    its 100 pairs drawn uniformly without replacement."""
     from scipy.spatial.distance import cdist
-    order = np.argsort(cdist(q["desc"], lib), axis=1, kind="stable")[0, :TOPK]
-    for c in order[:n_pairs]:
-        cpu_pair(q, cads[int(c) % CAD_POOL])
-    return n_pairs
+    step = sweep.steps[step_index % len(sweep.steps)]
+    order = np.argsort(cdist(step["desc"], sweep.lib), axis=1, kind="stable")[:, :TOPK]
+    pairs = candidate_pairs(order, step)
+    chosen = rng.choice(len(pairs), n_pairs, replace=False)
+    for i in chosen:
+        qi, ci = pairs[int(i)]
+        cpu_pair(step["queries"][qi], sweep.cads[ci])
+    return [int(i) % TOPK for i in chosen]
 
 
 def run_reference(args, rank, world):
@@ -131,45 +186,51 @@ def run_reference(args, rank, world):
         return
     from oracle import ransac_c
     ransac_c.build()
-    lib, cads, queries = build_workload(0)
+    sweep = Sweep(0, args.feature_dim, args.warmup + args.steps)
+    rng = np.random.default_rng(SEED)  # same draw sequence as the cpu_baseline leg of the GPU arm
     for i in range(args.warmup):
-        cpu_step(lib, cads, queries[i % N_QUERIES], 1)
+        cpu_sample(sweep, i, rng, 1)
     t0 = time.perf_counter()
-    pairs = 0
+    ranks_drawn = []
     for i in range(args.steps):
-        pairs += cpu_step(lib, cads, queries[(args.warmup + i) % N_QUERIES], 1)
+        ranks_drawn += cpu_sample(sweep, args.warmup + i, rng, 1)
     dt = time.perf_counter() - t0
+    pairs = args.steps
     v = pairs / dt
     cores = os.cpu_count()
+    sample = (f"{pairs} pairs: per step one pair drawn uniformly (seed {SEED}) from the step's {PAIRS_PER_STEP} "
+              f"(query, top-10 candidate) pairs, after the step's retrieval; candidate ranks drawn: {ranks_drawn}; "
+              f"OpenMP threads {ransac_c.num_threads()}")
     print(json.dumps({
         "impl": "reference", "metric": "query-CAD pairs registered/sec", "value": v, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": "retrieval + the first of the 10 candidate pairs per step"},
-        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                         "sample": f"{pairs} pairs (1 per step) of the same workload, all host threads"},
+        "config": {"workload": WORKLOAD, "feature_dim": args.feature_dim, "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
-WORKERS = int(os.environ.get("CB_BENCH_WORKERS", "5"))  # host threads (each with its own cb_ctx + CUDA stream) registering a step's pairs
-
-
-def gpu_step(retrieval, symmetry, lib_in, cads_in, q, workers=WORKERS):
-    """One step through the public drop-in API; inputs are whatever the caller holds (CUDA tensors
-    for `value`, host NumPy for `e2e`).  The 10 candidate pairs are independent; sym_pose_many
-    registers them on `workers` host threads (workers=1: one after the other, as instrumented)."""
-    idx, _ = retrieval.topk(q["desc"], lib_in, TOPK)          # D2H of the 10 candidate ids
+# ------------------------------------------------------------------------------------ GPU arm
+def gpu_step(retrieval, symmetry, sweep, step, workers):
+    """One step through the public drop-in API; inputs are whatever the sweep holds (CUDA tensors for
+    `value`, host NumPy for `e2e`).  The step's pairs are independent; sym_pose_many registers them
+    concurrently (workers=1: one after the other, as instrumented)."""
+    idx, _ = retrieval.topk(step["desc"], sweep.lib, TOPK)     # D2H of the candidate ids
     jobs = []
-    for c in idx[0]:
-        cad = cads_in[int(c) % CAD_POOL]
+    for qi, ci in candidate_pairs(idx, step):
+        q, cad = step["queries"][qi], sweep.cads[ci]
         jobs.append(((q["F"], q["xyz"], cad["F"], cad["xyz"], cad["sym"]),
                      dict(k_nn=K_NN, max_corr=MAX_CORR, seed=SEED, rng=SEED)))
     return symmetry.sym_pose_many(jobs, workers=workers)
 
 
-def nbytes(*arrays):
-    return int(sum(a.size * a.itemsize for a in arrays))
+def load_peaks():
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peaks = json.load(open(pk_path)) if os.path.exists(pk_path) else {}
+    src = "measured" if peaks else "fallback"
+    return dict(hbm=peaks.get("hbm_gbs", 6650.0), bf16_burst=peaks.get("bf16_tflops", 1590.0),
+                bf16_sustained=peaks.get("bf16_tflops_sustained", 1400.0), src=src)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -178,18 +239,20 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    from corsair_b200 import get_context, retrieval, symmetry
+    from corsair_b200 import _capi, get_context, retrieval, symmetry
     ctx = get_context(local_rank)
-    lib, cads, queries = build_workload(rank)
-    lib_d = torch.from_numpy(lib).to(dev)
-    cads_d = [dict(F=torch.from_numpy(c["F"]).to(dev), xyz=torch.from_numpy(c["xyz"]).to(dev), sym=c["sym"]) for c in cads]
-    queries_d = [dict(desc=torch.from_numpy(q["desc"]).to(dev), F=torch.from_numpy(q["F"]).to(dev),
-                      xyz=torch.from_numpy(q["xyz"]).to(dev)) for q in queries]
-    queries_h = [dict(desc=torch.from_numpy(q["desc"]).pin_memory().numpy(), F=torch.from_numpy(q["F"]).pin_memory().numpy(),
-                      xyz=torch.from_numpy(q["xyz"]).pin_memory().numpy()) for q in queries]
+    workers = int(os.environ.get("CB_BENCH_WORKERS", "0")) or symmetry.DEFAULT_WORKERS
+    peaks = load_peaks()
+
+    up = lambda a: torch.from_numpy(a).to(dev)                       # noqa: E731
+    pin = lambda a: torch.from_numpy(a).pin_memory().numpy()         # noqa: E731
+    n_total = args.warmup + args.steps
+    sweep = Sweep(rank, args.feature_dim, n_total)
+    sweep_d, sweep_h = sweep.to(up), sweep.to(pin)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def barrier():
@@ -198,183 +261,285 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, lib_in, cads_in, qs, steps, warmup):
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(sw, steps, warmup, nworkers):
         for i in range(warmup):
-            fn(retrieval, symmetry, lib_in, cads_in, qs[i % N_QUERIES])
+            gpu_step(retrieval, symmetry, sw, sw.steps[i % len(sw.steps)], nworkers)
         barrier()
         evs = []
         for i in range(steps):
             flush.fill_(i & 0xff)  # L2 flush between timed iterations (outside the event pair)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            fn(retrieval, symmetry, lib_in, cads_in, qs[(warmup + i) % N_QUERIES])
+            gpu_step(retrieval, symmetry, sw, sw.steps[(warmup + i) % len(sw.steps)], nworkers)
             e1.record()
             evs.append((e0, e1))
         barrier()
-        ms = sum(a.elapsed_time(b) for a, b in evs)
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
 
-    import functools
-    from corsair_b200 import _capi
+    def copy_bytes():
+        a = b = 0
+        for c in _capi.all_contexts():
+            x, y = c.copy_bytes()
+            a, b = a + x, b + y
+        return a, b
+
+    count_launches = lambda: sum(c.launches() for c in _capi.all_contexts())  # noqa: E731
+
     # (1) instrumented pass, one pair after the other on one stream: per-class CUDA-event timing of
     #     the library's kernels (meaningless when several streams overlap) -> roofline, shares
-    seq_step = functools.partial(gpu_step, workers=1)
-    seq_step(retrieval, symmetry, lib_d, cads_d, queries_d[0])
+    inst_step = dict(desc=sweep_d.steps[0]["desc"][:2], queries=sweep_d.steps[0]["queries"][:2])  # 20 pairs
+    gpu_step(retrieval, symmetry, sweep_d, inst_step, 1)
     ctx.timing_reset()
     ctx.timing(True)
-    n_inst = max(1, min(2, args.steps))
-    for i in range(n_inst):
-        seq_step(retrieval, symmetry, lib_d, cads_d, queries_d[(1 + i) % N_QUERIES])
+    gpu_step(retrieval, symmetry, sweep_d, inst_step, 1)
     ctx.timing(False)
     classes = ctx.timing_read()
-    ms_seq = timed(seq_step, lib_d, cads_d, queries_d, n_inst, 0)
-    # (2) the timed runs: WORKERS host threads, each with its own context and stream
-    for w in range(2):
-        gpu_step(retrieval, symmetry, lib_d, cads_d, queries_d[w])  # create the worker contexts
-    count = lambda: sum(c.launches() for c in _capi.all_contexts())
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    gpu_step(retrieval, symmetry, sweep_d, inst_step, 1)
+    torch.cuda.synchronize()
+    ms_seq_pair = 1e3 * (time.perf_counter() - t0) / (2 * TOPK)
+
+    # (2) the timed runs
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ms_dev = timed(gpu_step, lib_d, cads_d, queries_d, args.steps, args.warmup)
+    ms_dev = timed(sweep_d, args.steps, args.warmup, workers)
     clocks = sampler.stop()
     barrier()
-    l0 = count()
-    gpu_step(retrieval, symmetry, lib_d, cads_d, queries_d[0])
+    l0 = count_launches()
+    gpu_step(retrieval, symmetry, sweep_d, sweep_d.steps[0], workers)
     barrier()
-    launches = (count() - l0) * args.steps  # library kernels of one step x timed steps
-    ms_e2e = timed(gpu_step, lib, cads, queries_h, args.steps, args.warmup)
-    # the same pairs without the per-query step boundary (BASELINE.json configs[2]'s shape at N_QUERIES
-    # queries per rank): one batched retrieval, then all N_QUERIES x TOPK pairs in ONE sym_pose_many call
-    def sweep():
-        desc = torch.cat([q["desc"] for q in queries_d])
-        idx, _ = retrieval.topk(desc, lib_d, TOPK)
-        jobs = []
-        for qi, q in enumerate(queries_d):
-            for c in idx[qi]:
-                cad = cads_d[int(c) % CAD_POOL]
-                jobs.append(((q["F"], q["xyz"], cad["F"], cad["xyz"], cad["sym"]),
-                             dict(k_nn=K_NN, max_corr=MAX_CORR, seed=SEED, rng=SEED)))
-        return symmetry.sym_pose_many(jobs, workers=WORKERS)
-    sweep()
-    barrier()
-    se0, se1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    flush.fill_(1)
-    se0.record()
-    sweep()
-    se1.record()
-    barrier()
-    t_sw = torch.tensor([se0.elapsed_time(se1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t_sw, op=dist.ReduceOp.MAX)
-    sweep_pairs_s = world * N_QUERIES * TOPK / (float(t_sw.item()) * 1e-3)
-    pairs = world * args.steps * TOPK
-    value = pairs / (ms_dev * 1e-3)
-    e2e = pairs / (ms_e2e * 1e-3)
+    launches_per_step = count_launches() - l0
+    h0, d0 = copy_bytes()
+    ms_e2e = timed(sweep_h, args.steps, args.warmup, workers)
+    h1, d1 = copy_bytes()
+    h2d_step, d2h_step = (h1 - h0) / n_total, (d1 - d0) / n_total
+    pairs = world * args.steps * PAIRS_PER_STEP
+    value, e2e = pairs / (ms_dev * 1e-3), pairs / (ms_e2e * 1e-3)
+
+    # (3) the same sweep at the feature width the shipped scripts use (evaluation.py:183)
+    d16 = None
+    if args.feature_dim != 16 and not args.quick:
+        n16 = max(2, min(6, args.steps))
+        s16 = Sweep(rank, 16, n16 + 1).to(up)
+        ms16 = timed(s16, n16, 1, workers)
+        d16 = {"value": world * n16 * PAIRS_PER_STEP / (ms16 * 1e-3), "unit": "pairs/s", "feature_dim": 16, "steps": n16,
+               "ms_per_step": ms16 / n16, "workload": "the C3 sweep with 16-d per-point features (evaluation.py:183), device-resident"}
+        del s16
+
+    extra = {} if args.quick else side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, max_over_ranks)
     if rank != 0:
         return
 
-    peaks = {}
-    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(pk_path):
-        peaks = json.load(open(pk_path))
-    hbm = peaks.get("hbm_gbs", 6650.0)
-    bf16 = peaks.get("bf16_tflops_sustained", 1400.0)
-    src = "measured" if peaks else "fallback"
+    # ---- roofline of the kernel class with the largest device time in the sequential pass
+    tracked = {k: v for k, v in classes.items() if v[2] > 0 and k != "ransac_waves"}
+    top = max(("knn_candidates", "ransac_score"), key=lambda k: tracked.get(k, (0, 0, 0))[0])
+    ms_k, work_k, n_k = tracked[top]
     traffic = {}
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_path):
         traffic = json.load(open(tr_path))
-    tracked = {k: v for k, v in classes.items() if v[2] > 0}
-    top = max(("knn_candidates", "ransac_score"), key=lambda k: tracked.get(k, (0, 0, 0))[0])
-    ms_k, work_k, n_k = tracked[top]
     if top == "ransac_score":
-        roof = {"bound": "hbm", "kernel": "ransac_tc_score_kernel (" + ctx.ransac_variant() + ")",
-                "achieved": work_k / (ms_k * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-                "note": f"effective streamed bytes (hypotheses scored x M x 32 B, BASELINE.json's definition); peak = {src} "
-                        "HBM copy bandwidth.  The correspondences live in L2/shared memory, so frac > 1; the kernel is "
-                        "a split-bf16 GEMM (K = 96) whose accumulators are drained by tcgen05.ld beside the next tile's "
-                        "MMAs: evals_per_clk_per_sm against the tensor pipe's 42.7 (12 MMAs x 64 clk per 32768 "
-                        "evaluations) is tensor_frac; with its arithmetic compiled out the kernel still needs 70 % of "
-                        "its time (profiles/r01_tmem_ld_microbench.txt)",
-                "evals_per_s": work_k / 32.0 / (ms_k * 1e-3)}
-        roof["evals_per_clk_per_sm"] = roof["evals_per_s"] / (148 * (clocks.get("sm_mhz") or 1965.0) * 1e6)
-        roof["tensor_frac"] = roof["evals_per_clk_per_sm"] / (128.0 * 128.0 * 2 / (12 * 64.0))
+        evals_s = work_k / (ms_k * 1e-3)
+        waves = max(1.0, classes["ransac_waves"][1])
+        kk = ctx.ransac_k()
+        roof = {"bound": "tensor", "kernel": "ransac_tc_score_kernel (" + ctx.ransac_variant() + ")",
+                "achieved": evals_s * 2.0 * kk / 1e12, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
+                "note": f"issued bf16 flop: (hypothesis, correspondence) evaluations/s x 2 x K, K = {kk} columns of the split "
+                        f"inner product; evaluations counted on the device for the CTAs that ran; peak = {peaks['src']} "
+                        "bf16 dense burst (the kernel is timed launch by launch in the sequential pass)",
+                "evals_per_s": evals_s, "effective_gbs": evals_s * 32.0 / 1e9,
+                "effective_gbs_note": "BASELINE.json's H x M x 32 B per second; the operands are L2/shared-memory resident, "
+                                      "so this is not an HBM fraction (dram traffic below)",
+                "launches": int(waves), "avg_launch_us": 1e3 * ms_k / waves,
+                "launches_skipped": int(n_k - waves)}
+        roof["evals_per_clk_per_sm"] = evals_s / (148 * (clocks.get("sm_mhz") or 1965.0) * 1e6)
     else:
         roof = {"bound": "tensor", "kernel": "knn candidates (" + ctx.knn_variant() + ")",
-                "achieved": work_k / (ms_k * 1e-3) / 1e12, "peak": bf16 / 3.0, "unit": "TFLOP/s",
-                "note": f"2*N0*N1*D flop; peak = {src} sustained bf16 dense / 3 (split-bf16 issues 3 products)"}
+                "achieved": work_k / (ms_k * 1e-3) / 1e12, "peak": peaks["bf16_sustained"] / 3.0, "unit": "TFLOP/s",
+                "note": f"2*N0*N1*D flop; peak = {peaks['src']} sustained bf16 dense / 3 (split-bf16 issues 3 products)",
+                "launches": n_k, "avg_launch_us": 1e3 * ms_k / max(1, n_k)}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof["traffic"] = traffic.get(top)
-    roof["launches"] = n_k
-    roof["avg_launch_us"] = 1e3 * ms_k / max(1, n_k)
     total_tracked = sum(v[0] for v in tracked.values())
     shares = {k: {"ms": round(v[0], 3), "launches": v[2], "share_of_tracked": round(v[0] / max(total_tracked, 1e-9), 4)}
               for k, v in tracked.items()}
 
-    # the metric's second half: the feature-kNN distance GEMM against the split-precision tensor peak, on
-    # the largest single-pair shape BASELINE.json names (configs[4]: 50k-point scan vs a 10k-point CAD)
-    from corsair_b200 import find_nn
-    g = torch.Generator(device=dev).manual_seed(5)
-    fa = torch.nn.functional.normalize(torch.randn(50000, D_FEAT, device=dev, generator=g), dim=1)
-    fb = torch.nn.functional.normalize(torch.randn(10000, D_FEAT, device=dev, generator=g), dim=1)
-    for _ in range(3):
-        find_nn.knn_device(fa, fb, K_NN)
-    ke0, ke1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    ke0.record()
-    for _ in range(10):
-        find_nn.knn_device(fa, fb, K_NN)
-    ke1.record()
-    torch.cuda.synchronize()
-    knn_tf = 2.0 * 50000 * 10000 * D_FEAT / (ke0.elapsed_time(ke1) / 10 * 1e-3) / 1e12
-    knn_tensor = {"shape": f"50000 x 10000, D = {D_FEAT}, k = {K_NN}", "achieved": knn_tf, "unit": "TFLOP/s",
-                  "peak": bf16 / 3.0, "frac": knn_tf / (bf16 / 3.0), "us_per_call": ke0.elapsed_time(ke1) / 10 * 1e3,
-                  "note": "whole cb_knn call (norms, packing, two-pass tcgen05 candidate kernel, exact re-rank), 2*N0*N1*D "
-                          f"flop; peak = {src} sustained bf16 dense / 3 products.  Every score is read out of tensor "
-                          "memory twice, beside the MMAs' accumulator traffic (measured 88-125 B/clk/SM), which caps this "
-                          "near 22-31 % of that peak (DESIGN.md K1)"}
-    del fa, fb
-
     cpu_base = None
-    if world == 1:
+    if world == 1 and not args.quick:
         from oracle import ransac_c
         ransac_c.build()
-        cpu_step(lib, cads, queries[0], 1)  # warm the KD-tree / BLAS / OpenMP pools
+        rng = np.random.default_rng(SEED)
+        cpu_sample(sweep, 0, rng, 1)  # warm the KD-tree / BLAS / OpenMP pools
         t0 = time.perf_counter()
-        n = 0
-        while n < 3 or (time.perf_counter() - t0 < 12 and n < 10):
-            n += cpu_step(lib, cads, queries[n % N_QUERIES], 1)
+        n, drawn = 0, []
+        while n < 3 or (time.perf_counter() - t0 < 15 and n < 8):
+            drawn += cpu_sample(sweep, 1 + n, rng, 1)
+            n += 1
         dt = time.perf_counter() - t0
         cpu_base = {"value": n / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
-                    "sample": f"{n} pairs of the same workload (retrieval + first candidate per query), all host threads"}
+                    "sample": f"{n} pairs of the same sweep, one drawn uniformly (seed {SEED}) from each of {n} steps' "
+                              f"{PAIRS_PER_STEP} pairs after that step's retrieval; candidate ranks drawn {drawn}; "
+                              f"OpenMP threads {ransac_c.num_threads()}"}
 
-    h2d = nbytes(queries[0]["desc"]) + TOPK * (nbytes(queries[0]["F"], queries[0]["xyz"]) +
-                                               int(np.mean([nbytes(c["F"], c["xyz"]) for c in cads]))) + nbytes(lib)
-    # per pair: the two seed-row draws and k-means++ draws go up (cb_sym_pose's staging), the segment
-    # offsets and the 1 + P poses / Chamfer values come back
-    h2d += TOPK * (2 * 100 * 4 + 10 * 4 + 10 * 1 * 2 * 8)
-    d2h = TOPK * 8 * 2 + TOPK * (16 * 4 + 3 * 17 * 8)
     print(json.dumps({
         "metric": "query-CAD pairs registered/sec", "value": value, "unit": "pairs/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 search / f64 re-rank, fit and in-band scoring",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "db": L_DB, "descriptor_dim": D_DESC, "feature_dim": D_FEAT, "k_nn": K_NN,
+        "config": {"workload": WORKLOAD, "db": L_DB, "descriptor_dim": D_DESC, "feature_dim": args.feature_dim, "k_nn": K_NN,
+                   "pairs_per_step_per_rank": PAIRS_PER_STEP, "pairs_timed": pairs,
                    "ransac": "budget 100000, adaptive stop (confidence 0.999), ransac_n 10, max_corr 0.2",
-                   "points_per_cloud": "2.6k-4.3k after 0.03 voxel dedup of 10k", "cad_pool": CAD_POOL,
-                   "l2": "256 MiB flush between timed steps", "host_threads": WORKERS,
-                   "sequential_ms_per_step": ms_seq / n_inst, "sharding": f"queries sharded over {world} rank(s), no data-path collective"},
-        "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "roofline": roof, "knn_tensor": knn_tensor,
-        "sweep": {"value": sweep_pairs_s, "unit": "pairs/s",
-                  "workload": f"the same pairs without the per-query step boundary: {N_QUERIES} queries per rank, one batched "
-                              f"retrieval, {N_QUERIES * TOPK} pairs in one sym_pose_many call (configs[2]'s shape)"},
-        "kernel_classes": shares,
-        "cpu_baseline": cpu_base,
-        "clocks": clocks}))
+                   "points_per_cloud_after_0.03_dedup": sweep.point_counts(), "cad_pool": CAD_POOL,
+                   "l2": "256 MiB flush between timed steps", "driver": symmetry.driver_name(), "concurrency": workers,
+                   "sequential_ms_per_pair": ms_seq_pair,
+                   "sharding": f"queries sharded over {world} rank(s), no data-path collective"},
+        "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d_step,
+                "d2h_bytes_per_step": d2h_step, "bytes": "counted where the copies are made (Context.dev / Context.host / "
+                                                           "the library's own staging), averaged over warm-up + timed steps"},
+        "gpu_launches": launches_per_step * args.steps, "launches_per_pair": launches_per_step / PAIRS_PER_STEP,
+        "roofline": roof, "kernel_classes": shares, "d16": d16, **extra,
+        "cpu_baseline": cpu_base, "clocks": clocks}))
+
+
+def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, max_over_ranks):
+    """C5, C4, the three sharded exchanges and the kNN tensor figure (see the module docstring)."""
+    import torch
+    from corsair_b200 import dist as cdist_mod, eval_pose, find_nn, pc_dist, retrieval, symmetry, synth
+    out = {}
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+
+    # ---- kNN distance GEMM against the split-precision tensor peak, on the largest single-pair shape
+    #      BASELINE.json names (configs[4]: 50k-point scan vs a 10k-point CAD); result checked below
+    g = torch.Generator(device=dev).manual_seed(5)
+    knn_t = {}
+    for d in (32, 16):
+        fa = torch.nn.functional.normalize(torch.randn(50000, d, device=dev, generator=g), dim=1)
+        fb = torch.nn.functional.normalize(torch.randn(10000, d, device=dev, generator=g), dim=1)
+        for _ in range(3):
+            idx = find_nn.knn_device(fa, fb, K_NN)
+        e0, e1 = ev(), ev()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(10):
+            idx = find_nn.knn_device(fa, fb, K_NN)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / 10 * 1e3
+        fb_rows = ctx.knn_last_fallback_rows()
+        # the timed call's answer against exact fp64 brute force on a sample of rows (torch, on the device)
+        rows = torch.arange(0, 50000, 97, device=dev)
+        d2 = torch.cdist(fa[rows].double(), fb.double()) ** 2
+        ok = bool((torch.gather(d2, 1, idx[rows]) <= torch.topk(d2, K_NN, largest=False).values * (1 + 1e-9) + 1e-12).all())
+        tf = 2.0 * 50000 * 10000 * d / (us * 1e-6) / 1e12
+        knn_t[f"d{d}"] = {"shape": f"50000 x 10000, D = {d}, k = {K_NN}", "achieved": tf, "unit": "TFLOP/s",
+                          "peak": peaks["bf16_sustained"] / 3.0, "frac": tf / (peaks["bf16_sustained"] / 3.0), "us_per_call": us,
+                          "fallback_rows": fb_rows, "checked_rows_ok": ok}
+        del fa, fb, d2
+    out["knn_tensor"] = dict(knn_t["d32"], d16=knn_t["d16"],
+                             note="whole cb_knn call (packing, tcgen05 candidate kernel, exact re-rank), 2*N0*N1*D flop; "
+                                  f"peak = {peaks['src']} sustained bf16 dense / 3 products")
+
+    # ---- C5: table category, pos_sym from the real histogram, 50k-point scans, 4096 hypotheses
+    labels = np.repeat(list(TABLE_SYM_HIST), list(TABLE_SYM_HIST.values()))
+    lrng = np.random.default_rng(900 + rank)
+    n_c5 = 6
+    c5 = []
+    for i in range(n_c5):
+        p = synth.make_pair(500 + 10 * rank + i, args.feature_dim, "table", n_raw=50000, n_cad=10000)
+        sym = int(lrng.choice(labels))
+        c5.append(((torch.from_numpy(p["baseF"]).to(dev), torch.from_numpy(p["xyz0"]).to(dev),
+                    torch.from_numpy(p["posF"]).to(dev), torch.from_numpy(p["xyz1"]).to(dev), sym),
+                   dict(k_nn=K_NN, max_corr=MAX_CORR, seed=SEED, rng=SEED, n_hypotheses=4096)))
+    symmetry.sym_pose_many(c5, workers=workers)
+    barrier()
+    e0, e1 = ev(), ev()
+    e0.record()
+    res = symmetry.sym_pose_many(c5, workers=workers)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    symmetry.sym_pose_many(c5[:2], workers=1)
+    torch.cuda.synchronize()
+    ms_seq = 1e3 * (time.perf_counter() - t0) / 2
+    regs = [1 + (8 if j[0][4] >= 2 else 2) for j in c5]
+    out["c5"] = {"value": world * n_c5 / (ms * 1e-3), "unit": "pairs/s", "pairs_per_rank": n_c5, "ms": ms,
+                 "sequential_ms_per_pair": ms_seq, "registrations_per_pair": regs,
+                 "symmetry_ok": [bool(r[4]) for r in res],
+                 "workload": "C5: table, 50 000-point scan vs 10 000-point CAD (M = 250 000), 4096 hypotheses per RANSAC, pos_sym "
+                             "drawn from the real label histogram (K = 4 and nine registrations when >= 2), device-resident"}
+
+    # ---- e3: one C5-sized RANSAC (M = 250 000, H = 4096) with the hypothesis range split over the ranks
+    a = c5[0][0]
+    idx = find_nn.knn_device(a[0], a[2], K_NN)
+    si = torch.repeat_interleave(torch.arange(a[0].shape[0], device=dev), K_NN)
+    ti = idx.reshape(-1)
+    single = eval_pose.ransac_device(a[1], a[3], MAX_CORR, seed=SEED, src_idx=si, tgt_idx=ti, n_hypotheses=4096, adaptive=False)
+    for _ in range(2):
+        Tm, stm = cdist_mod.ransac_sharded(a[1], a[3], MAX_CORR, seed=SEED, n_hypotheses=4096, src_idx=si, tgt_idx=ti)
+    barrier()
+    e0, e1 = ev(), ev()
+    e0.record()
+    Tm, stm = cdist_mod.ransac_sharded(a[1], a[3], MAX_CORR, seed=SEED, n_hypotheses=4096, src_idx=si, tgt_idx=ti)
+    e1.record()
+    barrier()
+    same = bool(torch.equal(Tm, single["T"]) and torch.equal(stm[:3], single["stats"][:3]))
+    sharded = {"ransac_hypothesis_sharded": {"ms": max_over_ranks(e0.elapsed_time(e1)), "m": int(len(si)), "hypotheses": 4096,
+                                             "equal_to_single_gpu": same, "ranks": world}}
+
+    # ---- e2: retrieval of 1000 queries with the 6778 library rows split over the ranks
+    lib, q, _ = synth.descriptor_db(1000, L=L_DB, Q=1000, d=D_DESC)
+    lib_d, q_d = torch.from_numpy(lib).to(dev), torch.from_numpy(q).to(dev)
+    ref_i, ref_d = retrieval.topk(q_d, lib_d, TOPK)
+    cdist_mod.retrieval_topk_sharded(q_d, lib_d, TOPK)
+    barrier()
+    e0, e1 = ev(), ev()
+    e0.record()
+    gi, gd = cdist_mod.retrieval_topk_sharded(q_d, lib_d, TOPK)
+    e1.record()
+    barrier()
+    sharded["retrieval_db_sharded"] = {"ms": max_over_ranks(e0.elapsed_time(e1)), "queries": 1000, "library": L_DB, "k": TOPK,
+                                       "equal_to_single_gpu": bool(np.array_equal(gi, ref_i) and np.array_equal(gd, ref_d)),
+                                       "ranks": world}
+
+    # ---- C4 / e4: all-pairs Chamfer table, 6778 clouds x 2048 points, rows sharded over the ranks
+    crng = np.random.default_rng(77)
+    base = [synth.normalize_cloud(synth.make_chair(np.random.default_rng(300 + c), 4096), C4_P) for c in range(64)]
+    stack = np.stack([base[i % 64] + 0.02 * crng.standard_normal((C4_P, 3)).astype(np.float32) for i in range(C4_L)])
+    stack_d = torch.from_numpy(stack.astype(np.float32)).to(dev)
+    barrier()
+    t0 = time.perf_counter()
+    table = cdist_mod.chamfer_matrix_sharded(stack_d)
+    barrier()
+    sec = max_over_ranks(time.perf_counter() - t0)
+    rows = [0, 1, C4_L // 2, C4_L - 1]
+    ref_rows = np.stack([pc_dist.chamfer_rows_device(stack_d, r, r + 1).cpu().numpy()[0] for r in rows])
+    got = table[rows]
+    for k_, r in enumerate(rows):
+        ref_rows[k_, r] = got[k_, r]  # the diagonal convention (200) is the table's
+    n_pairs = C4_L * (C4_L - 1) // 2
+    evals = n_pairs * float(C4_P) * C4_P  # one distance tile feeds both directions
+    fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12
+    out["c4"] = {"value": n_pairs / sec, "unit": "cloud pairs/s", "seconds": sec, "clouds": C4_L, "points": C4_P, "ranks": world,
+                 "rows_equal_to_single_gpu": bool(np.array_equal(got, ref_rows)),
+                 "symmetric": bool(np.array_equal(table, table.T)), "diagonal": float(table[0, 0]),
+                 "roofline": {"bound": "fp32", "achieved": evals * 8 / sec / 1e12 / world, "unit": "TFLOP/s per GPU",
+                              "peak": fp32_peak, "frac": evals * 8 / sec / 1e12 / world / fp32_peak,
+                              "note": "8 flop per point-pair evaluation (SURVEY 8d), wall time of the whole sharded call incl. the "
+                                      "all-gather, the device->host read of the table and H + H^T; peak = nominal fp32 FMA rate "
+                                      "(148 SMs x 128 lanes x 2 x 1.965 GHz), no measured fp32 peak exists"},
+                 "workload": "C4: all-pairs Chamfer table (utils/pc_dist.py:61-99), row blocks over the ranks, one all-gather"}
+    sharded["chamfer_rows_sharded"] = {"seconds": sec, "equal_to_single_gpu": out["c4"]["rows_equal_to_single_gpu"], "ranks": world}
+    out["sharded"] = sharded
+    return out
 
 
 def main():
@@ -383,6 +548,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--feature-dim", type=int, default=32, choices=[16, 32])
+    ap.add_argument("--quick", action="store_true", help="headline + roofline only (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -33,6 +33,7 @@ SIGNATURES = {
     "cb_set_ransac_variant": (c_int, [c_void_p, c_int]),
     "cb_ransac_debug_dump": (c_int, [c_void_p, c_void_p, c_int]),
     "cb_knn_last_fallback_rows": (c_int, [c_void_p, c_void_p]),
+    "cb_copy_bytes": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]),
     "cb_timing_enable": (c_int, [c_void_p, c_int]),
     "cb_timing_read": (c_int, [c_void_p, c_int, ctypes.POINTER(c_double), ctypes.POINTER(c_double),
                                ctypes.POINTER(ctypes.c_int64)]),
@@ -75,7 +76,21 @@ SIGNATURES = {
                             c_void_p, c_void_p, c_int, ctypes.c_int64, c_int, c_void_p, c_void_p, c_int, c_int,
                             c_double, c_double, c_u64, c_int, c_int, c_double, c_void_p, c_void_p]),
     "cb_irls_pose": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "cb_sym_pose_many": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "cb_ransac_gemm_k": (c_int, []),
 }
+
+
+class SymJob(ctypes.Structure):
+    """struct cb_sym_job of include/corsair_b200.h."""
+    _fields_ = [("base_f", c_void_p), ("base_xyz", c_void_p), ("pos_f", c_void_p), ("pos_xyz", c_void_p),
+                ("n0", ctypes.c_int32), ("n1", ctypes.c_int32), ("d", ctypes.c_int32), ("pos_sym", ctypes.c_int32),
+                ("k_nn", ctypes.c_int32), ("n_samples", ctypes.c_int32), ("n_nn", ctypes.c_int32),
+                ("n_init", ctypes.c_int32), ("n_trials", ctypes.c_int32), ("h_total", ctypes.c_int32),
+                ("adaptive", ctypes.c_int32), ("reserved", ctypes.c_int32), ("np_seed", ctypes.c_int64),
+                ("h_samples_base", c_void_p), ("h_samples_pos", c_void_p), ("h_km_first", c_void_p),
+                ("h_km_unif", c_void_p), ("min_center", c_double), ("max_dist", c_double), ("confidence", c_double),
+                ("seed", c_u64), ("h_out", c_void_p)]
 
 
 def load_library():
@@ -119,6 +134,8 @@ class Context:
         if rc != 0 or not h:
             raise RuntimeError(f"cb_create failed with status {rc}")
         self.handle = h
+        self.h2d_bytes = 0  # counted where the copies are made: dev() / host()
+        self.d2h_bytes = 0
 
     def close(self):
         if getattr(self, "handle", None):
@@ -144,6 +161,13 @@ class Context:
     def launches(self):
         return int(self.lib.cb_launch_count(self.handle))
 
+    def copy_bytes(self):
+        """(host->device, device->host) bytes moved so far: the marshalling of this Context (dev /
+        host below) plus the staging copies the C library issued itself (cb_copy_bytes)."""
+        a, b = ctypes.c_int64(), ctypes.c_int64()
+        self.lib.cb_copy_bytes(self.handle, ctypes.byref(a), ctypes.byref(b))
+        return self.h2d_bytes + a.value, self.d2h_bytes + b.value
+
     def knn_variant(self):
         return self.lib.cb_knn_variant(self.handle).decode()
 
@@ -152,6 +176,9 @@ class Context:
 
     def ransac_variant(self):
         return self.lib.cb_ransac_variant(self.handle).decode()
+
+    def ransac_k(self):
+        return int(self.lib.cb_ransac_gemm_k())
 
     def set_ransac_variant(self, v):
         self.lib.cb_set_ransac_variant(self.handle, int(v))
@@ -167,7 +194,7 @@ class Context:
         return int(self.lib.cb_knn_last_fallback_rows(self.handle, c_void_p(stream)))
 
     TIMING_CLASSES = ("knn_candidates", "knn_rerank", "ransac_score", "ransac_fit", "chamfer_nn",
-                      "rows_select", "kmeans")
+                      "rows_select", "kmeans", "ransac_waves")
 
     def timing(self, on):
         self.lib.cb_timing_enable(self.handle, int(bool(on)))
@@ -191,7 +218,15 @@ class Context:
             t = x.detach()
         else:
             t = torch.from_numpy(np.ascontiguousarray(x))
+        if not t.is_cuda:
+            self.h2d_bytes += t.numel() * t.element_size()
         return t.to(device=self.device, dtype=dtype, non_blocking=False).contiguous()
+
+    def host(self, t):
+        """CUDA tensor -> NumPy (the device->host read of a result)."""
+        if t.is_cuda:
+            self.d2h_bytes += t.numel() * t.element_size()
+        return t.cpu().numpy()
 
     def empty(self, shape, dtype):
         return torch.empty(shape, dtype=dtype, device=self.device)

@@ -49,6 +49,9 @@ extern "C" int cb_destroy(cb_ctx* ctx) {
     for (auto e : ctx->sub_event) cudaEventDestroy(e);
     for (auto s : ctx->sub_stream) cudaStreamDestroy(s);
     for (auto c : ctx->sub) cb_destroy(c);
+    for (auto e : ctx->slot_event) cudaEventDestroy(e);
+    for (auto s : ctx->slot_stream) cudaStreamDestroy(s);
+    for (auto c : ctx->slots) cb_destroy(c);
     if (ctx->fork_event) cudaEventDestroy(ctx->fork_event);
     if (ctx->sync_event) cudaEventDestroy(ctx->sync_event);
     for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
@@ -60,6 +63,13 @@ extern "C" int cb_destroy(cb_ctx* ctx) {
 extern "C" const char* cb_last_error(const cb_ctx* ctx) { return ctx ? ctx->err : "null context"; }
 
 extern "C" int64_t cb_launch_count(const cb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int cb_copy_bytes(const cb_ctx* ctx, int64_t* h2d, int64_t* d2h) {
+    if (!ctx) return CB_EINVAL;
+    if (h2d) *h2d = ctx->h2d_bytes;
+    if (d2h) *d2h = ctx->d2h_bytes;
+    return CB_OK;
+}
 
 extern "C" int cb_set_knn_variant(cb_ctx* ctx, int variant) {
     if (!ctx || variant < 0 || variant > 2) return CB_EINVAL;

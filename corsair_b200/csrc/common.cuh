@@ -16,6 +16,7 @@ struct cb_ctx {
     size_t arena_bytes = 0;
     size_t arena_off = 0;       // bump pointer, reset at the start of every public call
     int64_t launches = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;  // host<->device copies the library itself issued (cb_copy_bytes)
     int knn_variant = 0;        // 0 auto, 1 simt, 2 tcgen05
     int ransac_variant = 0;     // 0 auto (tcgen05), 1 simt fp32, 2 tcgen05
     float* ransac_dump = nullptr;  // test hook: the tensor-core values U[h, c] of the next cb_ransac
@@ -38,6 +39,10 @@ struct cb_ctx {
     std::vector<cudaStream_t> sub_stream;
     std::vector<cudaEvent_t> sub_event;
     cudaEvent_t fork_event = nullptr;
+    // cb_sym_pose_many: contexts (own stream, arena, staging, internal streams) that hold the pairs in flight
+    std::vector<cb_ctx*> slots;
+    std::vector<cudaStream_t> slot_stream;
+    std::vector<cudaEvent_t> slot_event;
     cudaEvent_t sync_event = nullptr;  // blocking-sync event: the host thread sleeps instead of spinning
 };
 

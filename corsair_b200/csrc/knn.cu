@@ -12,7 +12,6 @@
 //   4. fallback: queued rows are solved by exact float64 brute force.
 // Engine E2 (anything else): exact float64 distance rows + per-row radix select (select.cu).
 #include "common.cuh"
-#include <stdlib.h>
 #include "knn_internal.cuh"
 
 #include <float.h>
@@ -139,9 +138,22 @@ __device__ __forceinline__ float knn_out_dist(double key, int metric) {
     return (float)key;
 }
 
-// one warp per query; ncand = S*KC <= 256 candidate slots (<= 8 per lane; unused slots hold -1).
+// (key, index) of a candidate as integers that order like the pair: the float64 key's bits made
+// monotone (negative keys occur for the inner-product metric)
+__device__ __forceinline__ unsigned long long knn_sortable(double key) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(key);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double knn_unsortable(unsigned long long s) {
+    return __longlong_as_double((long long)((s >> 63) ? (s & 0x7fffffffffffffffull) : ~s));
+}
+
+// one warp per query; ncand = S*KC <= 32*SL candidate slots (SL per lane; unused slots hold -1).
 // bound (optional, [nq, S]): per chunk a score no dropped reference of that chunk is below;
 // without it the chunk's last (worst kept) candidate score plays that role.
+// The k rounds of "smallest remaining (key, index)" are three warp-wide integer minima (REDUX) each:
+// high word of the key, low word among the lanes that match, index among those that still match.
+template <int SL>
 __global__ void __launch_bounds__(256)
 knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int d, int dq_stride,
                   int k, int metric, const int32_t* __restrict__ cand_idx, const float* __restrict__ cand_s,
@@ -155,43 +167,41 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int ncand = S * KC;
     const float* qp = q + (size_t)qi * dq_stride;
-    constexpr int SL = 8;
-    double key[SL];
+    unsigned long long key[SL];
     int id[SL];
 #pragma unroll
     for (int t = 0; t < SL; ++t) {
         int ci = lane + 32 * t;
-        id[t] = -1;
-        key[t] = INFINITY;
+        id[t] = 0x7fffffff;
+        key[t] = ~0ull;
         if (ci < ncand) {
             int j = cand_idx[(size_t)qi * ncand + ci];
             if (j >= 0) {
                 id[t] = j;
-                key[t] = knn_exact_key(qp, r + (size_t)j * dq_stride, d, maxdot);
+                key[t] = knn_sortable(knn_exact_key(qp, r + (size_t)j * dq_stride, d, maxdot));
             }
         }
     }
     double kth = 0.0;
     int found = 0;
     for (int round = 0; round < k; ++round) {
-        double bk = INFINITY;
-        int bj = 0x7fffffff, bt = -1;
+        unsigned long long bk = ~0ull;
+        int bj = 0x7fffffff;
 #pragma unroll
         for (int t = 0; t < SL; ++t)
-            if (id[t] >= 0 && knn_less(key[t], id[t], bk, bj)) { bk = key[t]; bj = id[t]; bt = t; }
-        double wk = bk;
-        int wj = bj;
-        for (int o = 16; o > 0; o >>= 1) {
-            double ok = __shfl_xor_sync(0xffffffffu, wk, o);
-            int oj = __shfl_xor_sync(0xffffffffu, wj, o);
-            if (knn_less(ok, oj, wk, wj)) { wk = ok; wj = oj; }
-        }
+            if (key[t] < bk || (key[t] == bk && id[t] < bj)) { bk = key[t]; bj = id[t]; }
+        const unsigned hi = (unsigned)(bk >> 32), lo = (unsigned)bk;
+        const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+        const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+        const bool tied = hi == mh && lo == ml;
+        const int wj = (int)__reduce_min_sync(0xffffffffu, tied ? (unsigned)bj : 0x7fffffffu);
         if (wj == 0x7fffffff) break;  // fewer than k candidates (cannot happen when k <= nr)
-        if (bt >= 0 && bj == wj) {
+        if (tied && bj == wj) {
 #pragma unroll
             for (int t = 0; t < SL; ++t)
-                if (t == bt) id[t] = -1;
+                if (id[t] == wj) { id[t] = 0x7fffffff; key[t] = ~0ull; }
         }
+        const double wk = knn_unsortable(((unsigned long long)mh << 32) | ml);
         if (lane == 0) {
             size_t o = (size_t)qi * k + round;
             if (idx64) idx64[o] = wj;
@@ -302,67 +312,91 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     const int dp = d <= 16 ? 16 : 32;
     const int KC = k <= 5 ? 8 : 16;
     // the tcgen05 variant collects every reference at or above a per-(query, chunk) threshold: up to
-    // LC = 3 KC list slots per chunk; the SIMT variant keeps exactly the KC best
+    // LC = 5 KC list slots per chunk; the SIMT variant keeps exactly the KC best
     const bool use_tc = ctx->knn_variant != 1;
-    const int LC = use_tc ? 3 * KC : KC;
-    // reference chunks: about one CTA per SM, chunks of whole 256-reference tiles, S*LC <= 256
-    static int waves_x2 = -1;  // CB_KNN_HALFWAVES: tuning knob, CTAs per SM x 2 the chunking aims at
-    if (waves_x2 < 0) { const char* e = getenv("CB_KNN_HALFWAVES"); waves_x2 = e ? atoi(e) : 2; }
-    int qblocks = cb_div_up(nq, 128);
-    int S = (waves_x2 * ctx->sm_count / 2) / qblocks;  // rounded down: no second round of CTAs
-    S = max(1, min(S, 256 / LC));
-    S = min(S, max(1, nr / 256));
-    int chunk = cb_div_up(nr, S);
-    chunk = (chunk + 255) & ~255;  // whole tensor-core column tiles (256 references) per chunk
-    S = cb_div_up(nr, chunk);
-
-    const float* qd = q;
-    const float* rd = r;
-    if (dp != d) {
-        float* qpad = cb_alloc_t<float>(ctx, (size_t)nq * dp);
-        float* rpad = cb_alloc_t<float>(ctx, (size_t)nr * dp);
-        if (!qpad || !rpad) return CB_ENOMEM;
-        knn_pad_kernel<<<cb_div_up((int)((size_t)nq * dp), 256), 256, 0, st>>>(q, nq, d, dp, qpad);
-        CB_LAUNCH_CHECK(ctx);
-        knn_pad_kernel<<<cb_div_up((int)((size_t)nr * dp), 256), 256, 0, st>>>(r, nr, d, dp, rpad);
-        CB_LAUNCH_CHECK(ctx);
-        qd = qpad;
-        rd = rpad;
+    const int LC = use_tc ? knn_cand_tc_list_slots(KC) : KC;
+    const int qblocks = cb_div_up(nq, 128);
+    int S, chunk;
+    if (use_tc) {
+        // reference chunks of whole 256-column tiles, S * LC <= 256 list slots per query: the S with the
+        // shortest makespan — rounds of CTAs (one per SM) x tile passes per chunk (+ a per-CTA constant
+        // for the prologue); ties go to the smaller S (fewer candidates to re-rank)
+        const int tiles = cb_div_up(nr, 256);
+        double best_cost = 1e300;
+        int best_tps = tiles;
+        for (int s_try = 1; s_try <= min(256 / LC, tiles); ++s_try) {
+            const int tps = cb_div_up(tiles, s_try);
+            const int ss = cb_div_up(tiles, tps);
+            const int rounds = cb_div_up(qblocks * ss, ctx->sm_count);
+            const double cost = rounds * (knn_cand_tc_passes(tps) + 1.5);
+            if (cost < best_cost - 1e-9) { best_cost = cost; best_tps = tps; }
+        }
+        chunk = best_tps * 256;
+        S = cb_div_up(nr, chunk);
+    } else {
+        S = ctx->sm_count / qblocks;  // about one CTA per SM, rounded down: no second round of CTAs
+        S = max(1, min(S, 256 / LC));
+        S = min(S, max(1, nr / 256));
+        chunk = cb_div_up(nr, S);
+        chunk = (chunk + 255) & ~255;
+        S = cb_div_up(nr, chunk);
     }
-    float* rn = cb_alloc_t<float>(ctx, nr);
+
     unsigned int* scal = cb_alloc_t<unsigned int>(ctx, 2);  // [0] rmax bits, [1] fallback count
     int32_t* ci = cb_alloc_t<int32_t>(ctx, (size_t)nq * S * LC);
-    float* cs = cb_alloc_t<float>(ctx, (size_t)nq * S * LC);
     float* bound = cb_alloc_t<float>(ctx, (size_t)nq * S);
     int32_t* fb = cb_alloc_t<int32_t>(ctx, nq);
-    if (!rn || !scal || !ci || !cs || !bound || !fb) return CB_ENOMEM;
+    if (!scal || !ci || !bound || !fb) return CB_ENOMEM;
     CB_CUDA(ctx, cudaMemsetAsync(scal, 0, 2 * sizeof(unsigned int), st));
     ctx->knn_fb_count = (const int*)(scal + 1);
-    knn_norms_kernel<<<cb_div_up(nr, 256), 256, 0, st>>>(rd, nr, dp, rn, scal);
-    CB_LAUNCH_CHECK(ctx);
-
     const int maxdot = metric == CB_KNN_MAXDOT;
     double gamma = (dp + 4) * 6.0e-8;
-    {
-    cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
+    // rows the exact kernels read: the caller's (stride d) for the tensor-core variant, zero-padded
+    // copies (stride dp) for the SIMT one
+    const float* qd = q;
+    const float* rd = r;
+    int stride = d;
+    float* cs = nullptr;
     if (use_tc) {
-        int rc = knn_cand_tc_launch(ctx, qd, nq, rd, rn, nr, dp, KC, LC, chunk, S, maxdot, ci, cs, bound, st);
+        cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
+        int rc = knn_cand_tc_launch(ctx, q, nq, r, nr, d, dp, KC, LC, chunk, S, maxdot, ci, bound, scal, st);
         if (rc) return rc;
         gamma = knn_cand_tc_gamma(dp);
     } else {
+        if (dp != d) {
+            float* qpad = cb_alloc_t<float>(ctx, (size_t)nq * dp);
+            float* rpad = cb_alloc_t<float>(ctx, (size_t)nr * dp);
+            if (!qpad || !rpad) return CB_ENOMEM;
+            knn_pad_kernel<<<cb_div_up((int)((size_t)nq * dp), 256), 256, 0, st>>>(q, nq, d, dp, qpad);
+            CB_LAUNCH_CHECK(ctx);
+            knn_pad_kernel<<<cb_div_up((int)((size_t)nr * dp), 256), 256, 0, st>>>(r, nr, d, dp, rpad);
+            CB_LAUNCH_CHECK(ctx);
+            qd = qpad;
+            rd = rpad;
+        }
+        stride = dp;
+        float* rn = cb_alloc_t<float>(ctx, nr);
+        cs = cb_alloc_t<float>(ctx, (size_t)nq * S * LC);
+        if (!rn || !cs) return CB_ENOMEM;
+        knn_norms_kernel<<<cb_div_up(nr, 256), 256, 0, st>>>(rd, nr, dp, rn, scal);
+        CB_LAUNCH_CHECK(ctx);
+        cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
         if (dp == 16 && KC == 8) launch_simt<16, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         else if (dp == 16) launch_simt<16, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         else if (KC == 8) launch_simt<32, 8>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         else launch_simt<32, 16>(qd, nq, rd, rn, nr, chunk, S, maxdot, ci, cs, st);
         CB_LAUNCH_CHECK(ctx);
     }
-    }
     cb_timed_scope tscope2(ctx, CB_T_KNN_RERANK, 0.0, st);
-    knn_rerank_kernel<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, dp, k, metric, ci, cs, S, LC,
-                                                       use_tc ? bound : nullptr, scal, gamma, idx, idx32, dist, fb,
-                                                       (int*)(scal + 1));
-    CB_LAUNCH_CHECK(ctx);
-    knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, dp, k, metric, fb,
+    {
+        const int SL = cb_div_up(S * LC, 32);
+        auto kern = SL <= 1 ? knn_rerank_kernel<1> : SL <= 2 ? knn_rerank_kernel<2> : SL <= 4 ? knn_rerank_kernel<4>
+                                                                                               : knn_rerank_kernel<8>;
+        kern<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, stride, k, metric, ci, cs, S, LC, use_tc ? bound : nullptr,
+                                               scal, gamma, idx, idx32, dist, fb, (int*)(scal + 1));
+        CB_LAUNCH_CHECK(ctx);
+    }
+    knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, stride, k, metric, fb,
                                                                      (int*)(scal + 1), idx, idx32, dist);
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;

@@ -7,14 +7,18 @@
 // scores, smaller is better) with their GLOBAL reference index in cand_idx (unused: -1 / +inf).
 // SIMT variant: LC = KC, the KC best in ascending order.
 
-// tcgen05 candidate pass (knn_tc.cu), d in {16,32}, KC in {8,16}, LC = 3 KC: every reference of the
-// chunk whose score is at or below the chunk's threshold (the KC-th best of its column-group minima,
-// so at least KC references qualify), in no particular order; bound[qi*S + c] = that threshold (no dropped
-// reference scores below it), -inf when more than LC qualified (the re-rank then sends the row to
-// the exact fallback).
-int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr,
-                       int d, int KC, int LC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s,
-                       float* bound, cudaStream_t st);
+// tcgen05 candidate pass (knn_tc.cu), dp in {16,32} (rows of width d <= dp are zero-filled by its packing
+// kernel), KC in {8,16}, LC = 5 KC: every reference of the chunk whose score is at or below the chunk's
+// threshold (the KC-th best of the column-group minima of the chunk's first half, so at least KC
+// references qualify), in no particular order; bound[qi*S + c] = that threshold (no dropped reference
+// scores below it), -inf when more than LC qualified (the re-rank then sends the row to the exact
+// fallback).  *rmax_bits (zeroed by the caller) receives the largest |r|^2 as fp32 bits.
+int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int dp, int KC, int LC,
+                       int chunk, int S, int maxdot, int32_t* cand_idx, float* bound, unsigned int* rmax_bits,
+                       cudaStream_t st);
+int knn_cand_tc_list_slots(int KC);
+// tile passes (MMA + drain of one 128 x 256 accumulator) one CTA of a `tiles`-tile chunk runs
+int knn_cand_tc_passes(int tiles);
 // relative error bound of the tcgen05 split-bf16 inner product: |err| <= gamma * |q| |r|
 double knn_cand_tc_gamma(int d);
 

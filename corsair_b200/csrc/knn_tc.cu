@@ -1,5 +1,5 @@
 // tcgen05 candidate pass of the kNN engine (K1): the distance GEMM on the 5th-generation tensor
-// cores in split precision, fused with the running top-KC of every query row.
+// cores in split precision, fused with a threshold top-k of every query row.
 //
 // Split-bf16 ("bf16x3"): q = qh + ql, r = rh + rl (bf16 each);  q.r ~= qh.rh + qh.rl + ql.rh.
 // The three products are ONE GEMM over a widened K axis:
@@ -10,24 +10,26 @@
 // knn.cu).  Error: |dot' - exact| <= 3*2^-18 |q||r| + fp32 accumulation, covered by
 // knn_cand_tc_gamma() in the re-rank's proof obligation.
 //
-// Pipeline per CTA (one 128-query tile x one reference chunk), 320 threads:
-//   warp 8  producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
-//   warp 9  one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
+// Pipeline per CTA (one 128-query tile x one reference chunk of T column tiles), 576 threads:
+//   warp 16 producer: cp.async.bulk (TMA engine) of pre-packed operand tiles -> shared memory
+//   warp 17 one elected thread issues tcgen05.mma (M=128, N=256, K=16 per instruction) into one
 //           of two 256-column TMEM accumulators and commits to mbarriers
-//   warps 0-7 epilogue: warp w drains lane quadrant w%4 (one query row per thread), column half w/4
-//           of every accumulator, tcgen05.ld 32 columns at a time — two warps per SM sub-partition,
-//           so one warp's tensor-memory load overlaps the other's arithmetic.  The two threads of a
-//           row merge their pass-1 lists through shared memory (same threshold as one thread over
-//           all columns would find) and share the row's candidate list through a shared counter.
-// The chunk's GEMM runs TWICE (the tensor pipe is nearly idle, the operands sit in L2):
-//   pass 1  per row, the maxima of column groups (16 or 8 columns) go through a branch-free
-//           sorted insertion into the row's KC best group maxima; their KC-th is the row's
-//           threshold tau: at least KC references of the chunk score at or above it
-//   pass 2  every reference with score >= tau is appended to the row's candidate list: a branch-free
-//           32-bit qualification mask per tcgen05.ld, then one short loop over its set bits.
-// A per-lane sorted top-k over all columns would make the warp take the insertion path whenever
-// ANY of its 32 rows inserts, i.e. for nearly every column of a cold list (measured: 1 400
-// instructions per 32 columns); the threshold form costs ~0.6 + ~4 instructions per element.
+//   warps 0-15 epilogue: warp w drains lane quadrant w%4 (one query row per thread), column
+//           quarter w/4 of every accumulator (two 32-column tcgen05.ld per stage) — four warps per
+//           SM sub-partition.  Round 1 ran 8 epilogue warps and ncu showed the kernel bound by the
+//           epilogue's dependent-issue latency (issue 40 %, tensor pipe 44 %, stall `wait` 1.9 per
+//           issue with two warps per scheduler), not by tensor memory.
+// Schedule of a chunk (T tiles): T0 = ceil(T/2) "threshold" steps, then T "collect" steps:
+//   threshold  the maxima of 16- (8-) column groups of the first T0 tiles go through a branch-free
+//              sorted insertion into the thread's KC best group maxima; the four threads of a row
+//              merge their lists through shared memory: the KC-th best is the row's threshold tau
+//              (at least KC references of the chunk reach it)
+//   collect    every reference of the chunk with score >= tau is appended to the row's candidate
+//              list: a packed subtract + funnel shift per column builds a 32-bit qualification
+//              mask per tcgen05.ld, then one short loop over its set bits.
+// Round 1 ran the threshold pass over ALL tiles (every score left tensor memory twice); a threshold
+// from half of the chunk lets ~2 KC references qualify instead of ~KC (list slots: 5 KC) and cuts
+// MMA + drain work from 2 T to 1.5 T tile passes.
 #include "common.cuh"
 #include "knn_internal.cuh"
 #include "tc_common.cuh"
@@ -39,7 +41,10 @@ namespace {
 constexpr int kTileM = 128;   // queries per CTA (TMEM lanes)
 constexpr int kTileN = 256;   // references per MMA / accumulator stage
 constexpr int kExtraK = 16;   // the norm block of the widened K axis
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;
+constexpr int kColParts = kEpiWarps / 4;      // threads per query row
+constexpr int kPartN = kTileN / kColParts;    // 64 columns per thread and stage
+constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = (kEpiWarps + 2) * 32;
 
 __host__ __device__ constexpr int kprime(int D) { return 3 * D + kExtraK; }
@@ -48,48 +53,110 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-// fp32 rows [n, D] -> packed bf16 operand tiles.  One thread per (row, 8-column group).
-// is_b: 0 = A layout (hi|hi|lo|ones), 1 = B layout (hi|lo|hi|-norm/2 split in three).
-// B rows are stored at the scrambled position (row * perm_a) mod n_pad (perm_a coprime to n_pad;
-// 1 for A): the column groups of the threshold pass then hold pseudo-random subsets of the
-// references, whatever spatial order (and feature similarity between neighbours) the cloud has.
-__global__ void knn_tc_pack_kernel(const float* __restrict__ x, const float* __restrict__ norms, int n, int n_pad,
-                                   int D, int TR, int is_b, int maxdot, unsigned perm_a,
-                                   __nv_bfloat16* __restrict__ out) {
-    const int KP = kprime(D);
-    const int groups = KP / 8;
-    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= (size_t)n_pad * groups) return;
-    const int row = (int)(gid / groups), kc = (int)(gid % groups);
-    __nv_bfloat16 v[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) v[e] = __float2bfloat16_rn(0.f);
-    const int k0 = kc * 8;
-    if (k0 < 3 * D) {
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// fp32 rows -> packed bf16 operand tiles, ONE launch for both operands (round 1: a norms kernel,
+// two pad kernels and two pack kernels).  One thread per padded row: rows [0, nq_pad) are queries (A
+// layout hi|hi|lo|ones, 128-row tiles), rows [nq_pad, nq_pad + nr_pad) references (B layout
+// hi|lo|hi|-norm/2 in three exact bf16 pieces, 256-row tiles).  Rows of width d < D are zero-filled.
+// B rows are stored at the scrambled position (row * perm_a) mod nr_pad (perm_a coprime to nr_pad):
+// the column groups of the threshold pass then hold pseudo-random subsets of the references,
+// whatever spatial order (and feature similarity between neighbours) the cloud has.  The largest
+// reference norm (fp32, the re-rank's error scale) goes to rmax_bits.
+template <int D>
+__global__ void __launch_bounds__(128)
+knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float* __restrict__ r, int nr, int nr_pad,
+                   int d, int maxdot, unsigned perm_a, __nv_bfloat16* __restrict__ Apack,
+                   __nv_bfloat16* __restrict__ Bpack, unsigned int* __restrict__ rmax_bits) {
+    constexpr int KP = kprime(D);
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool is_b = gid >= nq_pad;
+    const int row = is_b ? gid - nq_pad : gid;
+    float norm = 0.f;
+    if (row < (is_b ? nr_pad : nq_pad)) {
+        const int n = is_b ? nr : nq;
+        const float* x = (is_b ? r : q) + (size_t)row * d;
+        uint32_t hp[D / 2], lp[D / 2];  // bf16 pairs: hi and lo pieces of columns (2c, 2c + 1)
+        auto put = [&](int c2, float a, float b) {
+            __nv_bfloat16 ah, al, bh, bl;
+            tc::split2(a, ah, al);
+            tc::split2(b, bh, bl);
+            hp[c2] = (uint32_t)__bfloat16_as_ushort(ah) | ((uint32_t)__bfloat16_as_ushort(bh) << 16);
+            lp[c2] = (uint32_t)__bfloat16_as_ushort(al) | ((uint32_t)__bfloat16_as_ushort(bl) << 16);
+            norm = fmaf(a, a, norm);
+            norm = fmaf(b, b, norm);
+        };
         if (row < n) {
-            const int part = k0 / D;          // 0,1,2
-            const int c0 = k0 - part * D;     // column inside the part
-            const bool want_lo = is_b ? (part == 1) : (part == 2);
+            if (d == D) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                __nv_bfloat16 hi, lo;
-                tc::split2(x[(size_t)row * D + c0 + e], hi, lo);
-                v[e] = want_lo ? lo : hi;
+                for (int c = 0; c < D; c += 4) {
+                    const float4 v = *reinterpret_cast<const float4*>(x + c);
+                    put(c / 2, v.x, v.y);
+                    put(c / 2 + 1, v.z, v.w);
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < D; c += 2) put(c / 2, c < d ? x[c] : 0.f, c + 1 < d ? x[c + 1] : 0.f);
             }
-        }
-    } else if (k0 == 3 * D) {
-        if (!is_b) {
-            if (row < n) { v[0] = v[1] = v[2] = __float2bfloat16_rn(1.f); }
-        } else if (row < n) {
-            if (!maxdot) tc::split3(-0.5f * norms[row], v[0], v[1], v[2]);
         } else {
-            v[0] = __float2bfloat16_rn(-1e30f);  // padding references can never enter a list
+#pragma unroll
+            for (int c = 0; c < D / 2; ++c) hp[c] = lp[c] = 0u;
         }
+        // the norm block: A = (1, 1, 1, 0...), B = -|r|^2/2 in three exact bf16 pieces
+        uint32_t ex0 = 0u, ex1 = 0u;
+        if (!is_b) {
+            if (row < n) { ex0 = 0x3F803F80u; ex1 = 0x3F80u; }
+        } else if (row < n) {
+            if (!maxdot) {
+                __nv_bfloat16 c0, c1, c2;
+                tc::split3(-0.5f * norm, c0, c1, c2);
+                ex0 = (uint32_t)__bfloat16_as_ushort(c0) | ((uint32_t)__bfloat16_as_ushort(c1) << 16);
+                ex1 = (uint32_t)__bfloat16_as_ushort(c2);
+            }
+        } else {
+            ex0 = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(-1e30f));  // padding references can never enter a list
+        }
+        const int TR = is_b ? kTileN : kTileM;
+        const int prow = is_b ? (int)(((unsigned long long)row * perm_a) % (unsigned)nr_pad) : row;
+        const int tile = prow / TR, rr = prow % TR;
+        char* base = reinterpret_cast<char*>(is_b ? Bpack : Apack) + (size_t)tile * TR * KP * 2 +
+                     (size_t)(rr >> 3) * 128 + (size_t)(rr & 7) * 16;
+        const size_t kstride = (size_t)(TR / 8) * 128;  // tc::tile_offset: [kc][r/8][r%8][8 x bf16]
+#pragma unroll
+        for (int kc = 0; kc < KP / 8; ++kc) {
+            constexpr int kGroupsPerPart = D / 8;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (kc < 3 * kGroupsPerPart) {
+                const int part = kc / kGroupsPerPart, w0 = (kc % kGroupsPerPart) * 4;
+                const bool want_lo = is_b ? (part == 1) : (part == 2);
+                v.x = want_lo ? lp[w0] : hp[w0];
+                v.y = want_lo ? lp[w0 + 1] : hp[w0 + 1];
+                v.z = want_lo ? lp[w0 + 2] : hp[w0 + 2];
+                v.w = want_lo ? lp[w0 + 3] : hp[w0 + 3];
+            } else if (kc == 3 * kGroupsPerPart) {
+                v.x = ex0;
+                v.y = ex1;
+            }
+            *reinterpret_cast<uint4*>(base + kc * kstride) = v;
+        }
+        if (!(is_b && row < nr)) norm = 0.f;
     }
-    const int prow = (int)(((unsigned long long)row * perm_a) % (unsigned)n_pad);
-    const int tile = prow / TR, r = prow % TR;
-    char* dst = reinterpret_cast<char*>(out) + (size_t)tile * TR * KP * 2 + tc::tile_offset(TR, r, kc);
-    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+    // block max of the reference norms -> one atomic per warp (non-negative floats order like their bits)
+    for (int o = 16; o > 0; o >>= 1) norm = fmaxf(norm, __shfl_xor_sync(0xffffffffu, norm, o));
+    if ((threadIdx.x & 31) == 0 && norm > 0.f) atomicMax(rmax_bits, __float_as_uint(norm));
 }
 
 struct TcSmemCtl {
@@ -103,7 +170,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
               int chunk, int S, int maxdot, unsigned perm_inv, int nr_pad, int32_t* __restrict__ cand_idx,
               float* __restrict__ bound) {
     constexpr int KP = kprime(D);
-    constexpr int LC = 3 * KC;            // list slots per (query, chunk)
+    constexpr int LC = 5 * KC;            // list slots per (query, chunk): P(overflow) ~ 2e-5
     constexpr int GROUP = 128 / KC;       // columns per group maximum: 16 (KC = 8) or 8 (KC = 16)
     constexpr uint32_t A_BYTES = kTileM * KP * 2, B_BYTES = kTileN * KP * 2;
     constexpr uint32_t LBO_A = (kTileM / 8) * 128, LBO_B = (kTileN / 8) * 128;
@@ -111,14 +178,15 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
     unsigned char* sA = smem;
     unsigned char* sB = smem + A_BYTES;
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + 2 * B_BYTES);
-    float* s_top = reinterpret_cast<float*>(smem + A_BYTES + 2 * B_BYTES + 128);  // [2][kTileM][KC]
-    int* s_cnt = reinterpret_cast<int*>(s_top + 2 * kTileM * KC);                // [kTileM]
+    float* s_top = reinterpret_cast<float*>(smem + A_BYTES + 2 * B_BYTES + 128);  // [kColParts][kTileM][KC]
+    int* s_cnt = reinterpret_cast<int*>(s_top + kColParts * kTileM * KC);        // [kTileM]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c = blockIdx.y;
     const int t0 = (c * chunk) / kTileN;
     const int t1 = min((nr + kTileN - 1) / kTileN, ((c + 1) * chunk) / kTileN);
     const int ntiles = t1 - t0;
-    const int nsteps = 2 * ntiles;  // the chunk's tiles, twice
+    const int nthr = (ntiles + 1) >> 1;     // threshold steps: the first half of the chunk's tiles
+    const int nsteps = nthr + ntiles;       // then every tile once more (collect)
 
     if (threadIdx.x == 0) {
         tc::mbar_init(&ctl->a_full, 1);
@@ -144,7 +212,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             tc::bulk_g2s(sA, reinterpret_cast<const char*>(Apack) + (size_t)blockIdx.x * A_BYTES, A_BYTES, &ctl->a_full);
             for (int it = 0; it < nsteps; ++it) {
                 const int st = it & 1, use = it >> 1;
-                const int tile = t0 + (it >= ntiles ? it - ntiles : it);
+                const int tile = t0 + (it >= nthr ? it - nthr : it);
                 tc::mbar_wait(&ctl->empty[st], (use & 1) ^ 1);
                 tc::mbar_arrive_expect_tx(&ctl->full[st], B_BYTES);
                 tc::bulk_g2s(sB + st * B_BYTES, reinterpret_cast<const char*>(Bpack) + (size_t)tile * B_BYTES, B_BYTES,
@@ -174,50 +242,32 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             }
         }
     } else {
-        // ===== epilogue: 256 threads = 128 query rows (TMEM lanes) x 2 column halves =====
-        const int half = warp >> 2;
+        // ===== epilogue: 512 threads = 128 query rows (TMEM lanes) x 4 column quarters =====
+        const int part = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const int qi = blockIdx.x * kTileM + row;
         const size_t o = ((size_t)min(qi, nq - 1) * S + c) * LC;
         const bool live = qi < nq;
-        constexpr int kHalfN = kTileN / 2;
-        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + half * kHalfN;
+        const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + part * kPartN;
         float top[KC];  // the KC best group maxima of this thread's columns, descending
 #pragma unroll
         for (int t = 0; t < KC; ++t) top[t] = -INFINITY;
         float tau = -INFINITY;
+        f32x2 ntau2 = pk2(0.f, 0.f);
         for (int it = 0; it < nsteps; ++it) {
             const int st = it & 1, use = it >> 1;
-            const bool second = it >= ntiles;
-            if (it == ntiles) {
-                // the row's threshold: KC-th best of the union of both halves' group maxima
+            const bool collect = it >= nthr;
+            if (it == nthr) {
+                // the row's threshold: KC-th best of the union of its four threads' group maxima
 #pragma unroll
-                for (int t = 0; t < KC; ++t) s_top[(half * kTileM + row) * KC + t] = top[t];
-                named_bar_sync(1, kEpiWarps * 32);
+                for (int t = 0; t < KC; ++t) s_top[(part * kTileM + row) * KC + t] = top[t];
+                named_bar_sync(1, kEpiThreads);
 #pragma unroll
-                for (int u = 0; u < KC; ++u) {
-                    float x = s_top[((half ^ 1) * kTileM + row) * KC + u];
+                for (int p = 1; p < kColParts; ++p) {
+                    const float* other = s_top + (((part + p) % kColParts) * kTileM + row) * KC;
 #pragma unroll
-                    for (int t = 0; t < KC; ++t) {
-                        const float hi = fmaxf(top[t], x);
-                        x = fminf(top[t], x);
-                        top[t] = hi;
-                    }
-                }
-                tau = fmaxf(top[KC - 1], -1e29f);  // padding (-1e30) never qualifies
-            }
-            tc::mbar_wait(&ctl->tmem_full[st], use & 1);
-            tc::fence_after_sync();
-            const int col0 = (t0 + (second ? it - ntiles : it)) * kTileN + half * kHalfN;
-            // one 32-column chunk of this thread's half of the stage
-            auto process = [&](const float (&v)[32], int cb) {
-                if (!second) {
-#pragma unroll
-                    for (int g = 0; g < 32 / GROUP; ++g) {
-                        float x = v[g * GROUP];
-#pragma unroll
-                        for (int e = 1; e < GROUP; ++e) x = fmaxf(x, v[g * GROUP + e]);
-                        // branch-free insertion into the descending list (x sinks to its place)
+                    for (int u = 0; u < KC; ++u) {
+                        float x = other[u];
 #pragma unroll
                         for (int t = 0; t < KC; ++t) {
                             const float hi = fmaxf(top[t], x);
@@ -225,50 +275,74 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                             top[t] = hi;
                         }
                     }
-                } else {
-                    // which of the 32 columns qualify: a bit mask, two instructions per column on two
-                    // pipes — the sign bit of v - tau (set: below the threshold) is shifted into the word
-                    // by one funnel shift; column e lands at bit 31 - e, hence the bit reversal
+                }
+                tau = fmaxf(top[KC - 1], -1e29f);  // padding (-1e30) never qualifies
+                ntau2 = pk2(-tau, -tau);
+            }
+            tc::mbar_wait(&ctl->tmem_full[st], use & 1);
+            tc::fence_after_sync();
+            const int col0 = (t0 + (collect ? it - nthr : it)) * kTileN + part * kPartN;
+            // both 32-column loads of this thread's quarter, then the stage goes straight back to the
+            // MMA warp: the arithmetic below overlaps the other warps' loads and the next MMAs
+            float v[kPartN];
+            tc::tmem_ld32(lane_addr + st * kTileN, v);
+            tc::tmem_ld32(lane_addr + st * kTileN + 32, v + 32);
+            tc::tmem_ld_wait64(v);
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
+            if (!collect) {
+#pragma unroll
+                for (int g = 0; g < kPartN / GROUP; ++g) {
+                    // group maximum as a tree (FMNMX3 in SASS), then a branch-free insertion into the
+                    // descending list (x sinks to its place)
+                    float m[GROUP];
+#pragma unroll
+                    for (int e = 0; e < GROUP; ++e) m[e] = v[g * GROUP + e];
+#pragma unroll
+                    for (int w = GROUP / 2; w > 0; w >>= 1)
+#pragma unroll
+                        for (int e = 0; e < w; ++e) m[e] = fmaxf(m[e], m[e + w]);
+                    float x = m[0];
+#pragma unroll
+                    for (int t = 0; t < KC; ++t) {
+                        const float hi = fmaxf(top[t], x);
+                        x = fminf(top[t], x);
+                        top[t] = hi;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int h = 0; h < kPartN / 32; ++h) {
+                    // which of the 32 columns qualify: packed v - tau (two columns per instruction), the
+                    // sign bit (set: below the threshold) shifted into the word by one funnel shift;
+                    // column e lands at bit 31 - e, hence the bit reversal
                     unsigned below = 0;
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) below = __funnelshift_l(__float_as_uint(v[e] - tau), below, 1);
+                    for (int e = 0; e < 32; e += 2) {
+                        float d0, d1;
+                        unpk2(add2(pk2(v[h * 32 + e], v[h * 32 + e + 1]), ntau2), d0, d1);
+                        below = __funnelshift_l(__float_as_uint(d0), below, 1);
+                        below = __funnelshift_l(__float_as_uint(d1), below, 1);
+                    }
                     unsigned mask = __brev(~below);
                     // padding rows (all-equal scores) and rows whose list already overflowed (they go
                     // to the exact fallback whatever else qualifies) must not spin in the loop below
                     if (!live || (mask && *(volatile int*)&s_cnt[row] > LC)) mask = 0;
                     // append their reference indices (the re-rank recomputes every candidate exactly,
-                    // the approximate scores are not needed); ~1 % of the columns qualify
+                    // the approximate scores are not needed)
                     while (mask) {
                         const int e = __ffs(mask) - 1;
                         mask &= mask - 1;
                         const int pos = atomicAdd(&s_cnt[row], 1);
                         if (pos < LC)
-                            cand_idx[o + pos] = (int)(((unsigned long long)(col0 + cb * 32 + e) * perm_inv) % (unsigned)nr_pad);
+                            cand_idx[o + pos] = (int)(((unsigned long long)(col0 + h * 32 + e) * perm_inv) % (unsigned)nr_pad);
                     }
                 }
-            };
-            // software-pipelined drain: the next 32 columns are in flight while these are processed;
-            // the stage goes back to the MMA warp as soon as its last load has landed
-            static_assert(kHalfN / 32 == 4, "four chunks per stage and thread");
-            float va[32], vb[32];
-            tc::tmem_ld32(lane_addr + st * kTileN, va);
-            tc::tmem_ld_wait32(va);
-            tc::tmem_ld32(lane_addr + st * kTileN + 32, vb);
-            process(va, 0);
-            tc::tmem_ld_wait32(vb);
-            tc::tmem_ld32(lane_addr + st * kTileN + 64, va);
-            process(vb, 1);
-            tc::tmem_ld_wait32(va);
-            tc::tmem_ld32(lane_addr + st * kTileN + 96, vb);
-            process(va, 2);
-            tc::tmem_ld_wait32(vb);
-            tc::fence_before_sync();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[st]);
-            process(vb, 3);
+            }
         }
-        named_bar_sync(1, kEpiWarps * 32);  // both halves of every row have appended
-        if (live && half == 0) {
+        named_bar_sync(1, kEpiThreads);  // every thread of every row has appended
+        if (live && part == 0) {
             const int cnt = s_cnt[row];
             for (int t = min(cnt, LC); t < LC; ++t) cand_idx[o + t] = -1;
             // no dropped reference scores below the threshold; an overflowing list proves nothing
@@ -284,7 +358,7 @@ template <int D, int KC>
 cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
                       unsigned perm_inv, int nr_pad, int32_t* ci, float* bound, cudaStream_t st) {
     constexpr int KP = kprime(D);
-    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + 128 + 2 * kTileM * KC * 4 + kTileM * 4 + 64;
+    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + 128 + kColParts * kTileM * KC * 4 + kTileM * 4 + 64;
     cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((nq + kTileM - 1) / kTileM, S);
@@ -300,18 +374,22 @@ extern "C" const char* cb_knn_variant(const cb_ctx* ctx) {
     return (ctx && ctx->knn_variant == 1) ? "simt" : "tcgen05";
 }
 
-int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, const float* rn, int nr, int d, int KC,
-                       int LC, int chunk, int S, int maxdot, int32_t* cand_idx, float* cand_s, float* bound,
+int knn_cand_tc_list_slots(int KC) { return 5 * KC; }
+
+// tile passes (MMA + drain of one 128 x 256 accumulator) one CTA of a `tiles`-tile chunk runs
+int knn_cand_tc_passes(int tiles) { return tiles + (tiles + 1) / 2; }
+
+// q [nq, d], r [nr, d] raw rows (d <= dp, dp in {16, 32}); writes *rmax_bits (zeroed by the caller)
+int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int dp, int KC, int LC,
+                       int chunk, int S, int maxdot, int32_t* cand_idx, float* bound, unsigned int* rmax_bits,
                        cudaStream_t st) {
-    if ((d != 16 && d != 32) || (KC != 8 && KC != 16) || LC != 3 * KC || chunk % kTileN != 0)
+    if ((dp != 16 && dp != 32) || d > dp || (KC != 8 && KC != 16) || LC != 5 * KC || chunk % kTileN != 0)
         CB_FAIL(ctx, CB_EUNSUPPORTED, "knn_cand_tc_launch: unsupported shape (d=%d KC=%d LC=%d chunk=%d)", d, KC, LC, chunk);
-    const int KP = kprime(d);
+    const int KP = kprime(dp);
     const int nq_pad = cb_div_up(nq, kTileM) * kTileM, nr_pad = cb_div_up(nr, kTileN) * kTileN;
     __nv_bfloat16* A = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nq_pad * KP);
     __nv_bfloat16* B = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nr_pad * KP);
     if (!A || !B) return CB_ENOMEM;
-    const int groups = KP / 8;
-    (void)cand_s;
     // multiplicative scramble of the reference rows: perm_a ~ 0.618 n_pad, coprime to n_pad
     unsigned perm_a = ((unsigned)(0.6180339887 * nr_pad)) | 1u, perm_inv = 1;
     for (;; perm_a += 2) {
@@ -319,15 +397,15 @@ int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, cons
         while (g1) { long long qq = g0 / g1, t = g0 - qq * g1; g0 = g1; g1 = t; t = x0 - qq * x1; x0 = x1; x1 = t; }
         if (g0 == 1) { perm_inv = (unsigned)((x0 % nr_pad + nr_pad) % nr_pad); perm_a %= (unsigned)nr_pad; break; }
     }
-    knn_tc_pack_kernel<<<(unsigned)(((size_t)nq_pad * groups + 255) / 256), 256, 0, st>>>(q, nullptr, nq, nq_pad, d,
-                                                                                          kTileM, 0, maxdot, 1u, A);
-    CB_LAUNCH_CHECK(ctx);
-    knn_tc_pack_kernel<<<(unsigned)(((size_t)nr_pad * groups + 255) / 256), 256, 0, st>>>(r, rn, nr, nr_pad, d, kTileN, 1,
-                                                                                          maxdot, perm_a, B);
+    const unsigned pack_blocks = (unsigned)cb_div_up(nq_pad + nr_pad, 128);
+    if (dp == 16)
+        knn_tc_pack_kernel<16><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, rmax_bits);
+    else
+        knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, rmax_bits);
     CB_LAUNCH_CHECK(ctx);
     cudaError_t e;
-    if (d == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
-    else if (d == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    else if (dp == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
     else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
     else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
     ctx->launches++;

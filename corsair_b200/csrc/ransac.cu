@@ -432,7 +432,12 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
     const int budget_in = state->budget;
     const int prev_count = state->best_count;
     if (tid == 0) {
-        dev_work[CB_T_RANSAC_SCORE] += (double)w * (double)m * 32.0;  // bytes this wave streamed
+        // evaluations (hypothesis x correspondence) the scoring launch of this wave performed: its CTAs
+        // of 256 hypotheses whose first hypothesis lay below the budget it saw (= budget_in: the previous
+        // fold finished before that launch started)
+        const int scored = min(w, ((min(budget_in, h0 + w) - h0 + 255) / 256) * 256);
+        dev_work[CB_T_RANSAC_SCORE] += (double)scored * (double)m;
+        dev_work[CB_T_RANSAC_WAVES] += 1.0;
         s_stop = h0 + w;
     }
     // 1. totals into shared memory (independent loads, unrolled so they overlap)
@@ -602,11 +607,10 @@ static int ransac_wave_first() {
     return v;
 }
 static int ransac_wave_max(const cb_ctx* ctx) {
-    static int override_ctas = -1;  // CB_RANSAC_WAVE_CTAS: tuning knob (CTAs of 256 hypotheses per wave)
-    if (override_ctas < 0) {
+    static const int override_ctas = [] {  // CB_RANSAC_WAVE_CTAS: tuning knob (CTAs of 256 hypotheses per wave)
         const char* e = getenv("CB_RANSAC_WAVE_CTAS");
-        override_ctas = e ? atoi(e) : 0;
-    }
+        return e ? atoi(e) : 0;
+    }();
     const int ctas = override_ctas > 0 ? min(override_ctas, 160) : min(ctx->sm_count, 160);
     return max(ransac_wave_first(), ctas * 256);
 }
@@ -744,6 +748,8 @@ extern "C" int cb_set_ransac_variant(cb_ctx* ctx, int variant) {
 extern "C" const char* cb_ransac_variant(const cb_ctx* ctx) {
     return (ctx && ctx->ransac_variant == 1) ? "simt" : "tcgen05";
 }
+
+extern "C" int cb_ransac_gemm_k(void) { return kRtKP; }
 
 extern "C" int cb_ransac_debug_dump(cb_ctx* ctx, float* u_out, int ld) {
     if (!ctx || (u_out && ld <= 0)) return CB_EINVAL;

@@ -33,8 +33,9 @@ def topk_device(q, lib, k, metric="euclidean", exclude_self=0, self_offset=0, ct
 
 
 def topk(q, lib, k, metric="euclidean", exclude_self=0):
-    idx, dist = topk_device(q, lib, k, metric, exclude_self)
-    return idx.cpu().numpy().astype(np.int64), dist.cpu().numpy()
+    ctx = _capi.get_context()
+    idx, dist = topk_device(q, lib, k, metric, exclude_self, ctx=ctx)
+    return ctx.host(idx).astype(np.int64), ctx.host(dist)
 
 
 def _cosine_rows(descriptors, k):

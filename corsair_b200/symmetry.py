@@ -9,6 +9,7 @@ only draws the 100 seed points from the global NumPy RNG exactly like the refere
 (data-independent) RandomState(0) stream sklearn's k-means++ would consume, and applies the
 sequential acceptance rule to 100 rows of statistics.
 """
+import ctypes
 import functools
 
 import numpy as np
@@ -214,41 +215,90 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
 # Concurrent driver.  The reference registers its pairs one after the other (evaluation.py:297)
 # or under tqdm's thread_map (evaluation-shapenet.py:341); pairs are independent, and one pair's
 # chain of small dependent kernels (fit, fold, k-means: a handful of blocks each) cannot fill 148
-# SMs, so the drop-in offers the same loop on a few host threads, each with its own cb_ctx and
-# CUDA stream: the device overlaps one pair's latency-bound kernels with another pair's scoring.
-_pool = None
-_pool_workers = 0
-_worker_tls = __import__("threading").local()
+# SMs.  cb_sym_pose_many keeps `workers` pairs in flight from the calling thread alone (each pair on
+# its own internal streams; the thread polls their events and enqueues whichever pair can go on), so
+# the device overlaps one pair's latency-bound kernels with another pair's scoring and no host thread
+# spins in the driver.  (Round 1 ran this loop on a pool of Python threads.)
+DEFAULT_WORKERS = 8
 
 
-def _worker_run(device, ready, args, kwargs):
-    torch.cuda.set_device(device)
-    st = getattr(_worker_tls, "stream", None)
-    if st is None:
-        st = _worker_tls.stream = torch.cuda.Stream(device=device)
-    with torch.cuda.stream(st):
-        st.wait_event(ready)  # inputs were produced on the caller's stream
-        return sym_pose(*args, **kwargs)  # ends with its own device->host reads (stream-synchronised)
+def driver_name():
+    return "cb_sym_pose_many: one host thread, pairs in flight on internal streams, event polling"
 
 
-def sym_pose_many(jobs, workers=4):
+def _job_record(ctx, args, kwargs, dev, keep):
+    baseF, xyz0, posF, xyz1, pos_sym = args[:5]
+    kwargs = dict(zip(("k_nn", "max_corr", "seed"), args[5:]), **kwargs)  # sym_pose's positional order
+    k_nn, max_corr, seed = kwargs.get("k_nn", 5), kwargs.get("max_corr", 0.20), kwargs.get("seed", 0)
+    baseF_d, posF_d, xyz0_d, xyz1_d = dev(baseF), dev(posF), dev(xyz0), dev(xyz1)
+    n0, n1, d = baseF_d.shape[0], posF_d.shape[0], baseF_d.shape[1]
+    if n1 < k_nn:
+        raise ValueError(f"k_nn={k_nn} exceeds the {n1} target points")
+    np_seed = int(kwargs["rng"])
+    if not 0 <= np_seed < 2 ** 32:
+        raise ValueError("Seed must be between 0 and 2**32 - 1")
+    K = 4 if pos_sym >= 2 else 2
+    n_nn = min(N_NN, n0, n1)
+    first, unif, n_trials = _kmeanspp_draws(n_nn, K)
+    out = np.empty(40, np.float64)
+    keep += [baseF_d, posF_d, xyz0_d, xyz1_d, out]
+    vp = _capi.c_void_p
+    rec = _capi.SymJob(baseF_d.data_ptr(), xyz0_d.data_ptr(), posF_d.data_ptr(), xyz1_d.data_ptr(), n0, n1, d,
+                       int(pos_sym), int(k_nn), 100, n_nn, N_INIT, n_trials, int(kwargs.get("n_hypotheses", 100000)),
+                       int(bool(kwargs.get("adaptive", True))), 0, np_seed, None, None,
+                       first.ctypes.data_as(vp), unif.ctypes.data_as(vp), MIN_CENTER, float(max_corr), CONFIDENCE,
+                       int(seed) & 0xFFFFFFFFFFFFFFFF, out.ctypes.data_as(vp))
+    return rec, out, min(n0, n1) < 100
+
+
+def sym_pose_many(jobs, workers=DEFAULT_WORKERS):
     """Register independent pairs concurrently.  ``jobs``: iterable of ``(args, kwargs)`` for
-    sym_pose (pass ``rng=np.random.RandomState(seed)`` in kwargs for reproducible segmentations);
-    returns sym_pose's result tuples in job order.  ``workers <= 1`` runs them in the calling thread."""
-    global _pool, _pool_workers
+    sym_pose; returns sym_pose's result tuples in job order.  Jobs whose ``rng`` is an int seed (the
+    seed rows are then replayed inside the C call) go through ONE cb_sym_pose_many call that keeps
+    ``workers`` pairs in flight; a list containing any other kind of ``rng`` (a RandomState, or the
+    global NumPy stream the reference draws from) keeps its sequential draw order and is registered
+    one pair after the other.  Host arrays shared between jobs (one query against ten candidates) are
+    uploaded once per call."""
     jobs = list(jobs)
-    if workers <= 1 or len(jobs) <= 1:
+    if not jobs:
+        return []
+    if not all(isinstance(k.get("rng"), (int, np.integer)) for _, k in jobs):
         return [sym_pose(*a, **k) for a, k in jobs]
-    if _pool is None or _pool_workers != workers:
-        from concurrent.futures import ThreadPoolExecutor
-        if _pool is not None:
-            _pool.shutdown(wait=True)
-        _pool = ThreadPoolExecutor(max_workers=workers, thread_name_prefix="corsair_b200")
-        _pool_workers = workers
-    device = torch.cuda.current_device()
-    ready = torch.cuda.Event()
-    ready.record(torch.cuda.current_stream(device))
+    ctx = _capi.get_context()
+    cache = {}
+
+    def dev(x):
+        if isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.float32 and x.is_contiguous():
+            return x
+        key = id(x)
+        if key not in cache:
+            cache[key] = ctx.dev(x, torch.float32)
+        return cache[key]
+
+    keep, outs, small = [], [], []
+    recs = (_capi.SymJob * len(jobs))()
     # longest first: a pair with pos_sym >= 2 runs 9 registrations, the others 3 (utils/symmetry.py:303-356)
     order = sorted(range(len(jobs)), key=lambda i: 0 if jobs[i][0][4] >= 2 else 1)
-    futs = {i: _pool.submit(_worker_run, device, ready, *jobs[i]) for i in order}
-    return [futs[i].result() for i in range(len(jobs))]
+    slot_of = {}
+    for pos, i in enumerate(order):
+        recs[pos], out, sm = _job_record(ctx, jobs[i][0], jobs[i][1], dev, keep)
+        slot_of[i] = pos
+        outs.append(out)
+        small.append(sm)
+    status = (ctypes.c_int32 * len(jobs))()
+    ctx.call("cb_sym_pose_many", ctypes.cast(recs, _capi.c_void_p), len(jobs), int(workers),
+             ctypes.cast(status, _capi.c_void_p), ctx.stream)
+    results = []
+    for i in range(len(jobs)):
+        out = outs[slot_of[i]]
+        st = int(out[34])
+        why = None
+        if small[slot_of[i]]:
+            why = "Cannot take a larger sample than population when 'replace=False'"
+        elif st in (1, 2):
+            why = "'NoneType' object has no attribute 'cluster_centers_'"
+        if why is not None:
+            tqdm.write(f"symmetry failed use ransac: {why}")
+        T = torch.from_numpy(out[:34].astype(np.float32))
+        results.append((T[:16].reshape(4, 4), float(out[16]), T[17:33].reshape(4, 4), float(out[33]), why is None))
+    return results

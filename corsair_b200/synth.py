@@ -11,19 +11,28 @@ def _box(rng, n, lo, hi):
     return rng.uniform(lo, hi, (n, 3))
 
 
-def make_chair(rng, n_pts=15000):
-    """Mirror-symmetric (about x = 0) chair: seat, back rest, four legs."""
+def make_chair(rng, n_pts=15000, bulk=1.0):
+    """Mirror-symmetric (about x = 0) chair: seat, back rest, four legs.  ``bulk`` thickens the seat,
+    the back and the legs (and adds arm rests above 3): the same 10 000 raw points then fall into more
+    0.03-voxels, so clouds after de-duplication span the 2.6k-8.0k points SURVEY.md F5 measured on
+    the real ShapeNet chairs instead of sitting at the light end (bulk = 1: 3.6k-4.7k)."""
     w, dpt = rng.uniform(0.35, 0.5), rng.uniform(0.35, 0.5)
     seat_h, back_h, leg = rng.uniform(0.35, 0.5), rng.uniform(0.4, 0.7), rng.uniform(0.02, 0.04)
+    st, bt = min(0.04 * bulk, 0.6 * seat_h), min(0.05 * bulk, 1.5 * dpt)
+    leg = leg * (1.0 + 0.25 * (bulk - 1.0)) if bulk > 1.0 else leg
     parts = [
-        (0.35, [-w, seat_h - 0.04, -dpt], [w, seat_h, dpt]),
-        (0.35, [-w, seat_h, -dpt], [w, seat_h + back_h, -dpt + 0.05]),
+        (0.35, [-w, seat_h - st, -dpt], [w, seat_h, dpt]),
+        (0.35, [-w, seat_h, -dpt], [w, seat_h + back_h, -dpt + bt]),
     ]
     for sx in (-1, 1):
         for sz in (-1, 1):
             cx, cz = sx * (w - leg), sz * (dpt - leg)
-            parts.append((0.075, [cx - leg, 0, cz - leg], [cx + leg, seat_h - 0.04, cz + leg]))
-    pts = [_box(rng, max(1, int(f * n_pts)), lo, hi) for f, lo, hi in parts]
+            parts.append((0.075, [cx - leg, 0, cz - leg], [cx + leg, seat_h - st, cz + leg]))
+    if bulk > 3.0:
+        for sx in (-1, 1):
+            parts.append((0.1, [sx * w - 0.06, seat_h, -dpt], [sx * w + 0.06, seat_h + 0.25, dpt]))
+    tot = sum(f for f, _, _ in parts)
+    pts = [_box(rng, max(1, int(f / tot * n_pts)), lo, hi) for f, lo, hi in parts]
     pc = np.concatenate(pts)[:n_pts]
     return pc[rng.permutation(len(pc))].astype(np.float32)
 
@@ -84,16 +93,29 @@ def symmetric_features(pc, W, kind, noise, rng):
 
 
 def make_pair(seed, D=32, category="chair", n_raw=10000, voxel=0.03, dropout=0.2, jitter=0.005,
-              feat_noise=0.05):
+              feat_noise=0.05, bulk=1.0, n_cad=None):
     """One query-CAD pair: dict(baseF, xyz0, posF, xyz1, T_gt, pos_sym).  xyz1/posF is the CAD in its
     canonical frame, xyz0/baseF the moved, thinned, jittered query (T_gt maps query -> CAD)."""
     rng = np.random.default_rng(seed)
+    n_pts = max(15000, n_raw)
     if category == "chair":
-        raw, kind, sym = make_chair(rng), "mirror", 1
+        raw, kind, sym = make_chair(rng, n_pts, bulk), "mirror", 1
     else:
-        raw, kind, sym = make_table(rng), "rot4", 4
+        raw, kind, sym = make_table(rng, n_pts), "rot4", 4
     W = rng.standard_normal((4, D))
-    cad = voxel_dedup(normalize_cloud(raw, n_raw), voxel)
+    norm = normalize_cloud(raw, n_raw)
+    if n_cad is None:
+        cad = voxel_dedup(norm, voxel)
+    else:
+        # BASELINE.json configs[4]: a dense scan against a fixed-size CAD cloud, neither de-duplicated
+        cad = norm[rng.choice(len(norm), n_cad, replace=False)]
+        keep = np.ones(len(norm), bool)
+        q_can = norm + jitter * rng.standard_normal(norm.shape).astype(np.float32)
+        T = random_pose(rng)
+        xyz0 = (q_can @ T[:3, :3].T + T[:3, 3]).astype(np.float32)
+        return dict(baseF=symmetric_features(q_can, W, kind, feat_noise, rng), xyz0=xyz0,
+                    posF=symmetric_features(cad, W, kind, feat_noise, rng), xyz1=cad.astype(np.float32),
+                    T_gt=np.linalg.inv(T), pos_sym=sym)
     keep = rng.random(len(cad)) > dropout
     q_can = cad[keep] + jitter * rng.standard_normal((int(keep.sum()), 3)).astype(np.float32)
     T = random_pose(rng)  # canonical -> query frame

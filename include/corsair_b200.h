@@ -61,6 +61,8 @@ int cb_set_knn_variant(cb_ctx* ctx, int variant);
 /* RANSAC scoring variant: "tcgen05" (split-bf16 GEMM, default) or "simt" (packed fp32);
  * cb_set_ransac_variant: 0 = auto, 1 = simt, 2 = tcgen05; for tests/bench */
 const char* cb_ransac_variant(const cb_ctx* ctx);
+/* columns of the scoring GEMM's widened K axis (bf16 flop issued per evaluation = 2 x this) */
+int cb_ransac_gemm_k(void);
 int cb_set_ransac_variant(cb_ctx* ctx, int variant);
 /* test hook: the next cb_ransac calls of this ctx (tcgen05 variant) also store the raw
  * tensor-core values U[h, c] = d^2 - max_dist^2 (before the exact in-band re-decision) into the
@@ -74,8 +76,9 @@ int cb_knn_last_fallback_rows(cb_ctx* ctx, void* stream);
 /* ---- instrumentation for bench.py ---------------------------------------------------------
  * With timing enabled every launch of a tracked kernel class is bracketed by CUDA events on the
  * launching stream.  cb_timing_read synchronises the device and returns, per class, the summed
- * device time (ms), the algorithmic work launched (flop for the kNN candidate kernel, bytes for
- * RANSAC scoring: hypotheses actually scored x correspondences x 32 B) and the launch count. */
+ * device time (ms), the algorithmic work launched (flop for the kNN candidate kernel; for RANSAC
+ * scoring the (hypothesis, correspondence) evaluations of the CTAs that ran, counted on the device)
+ * and the launch count. */
 enum cb_timing_class {
     CB_T_KNN_CAND = 0,   /* kNN candidate pass (distance GEMM + running top-k) */
     CB_T_KNN_RERANK = 1, /* exact float64 re-rank + fallback */
@@ -84,8 +87,12 @@ enum cb_timing_class {
     CB_T_CHAMFER_NN = 4,
     CB_T_ROWS_SELECT = 5, /* exact rows + radix select (retrieval, 50-NN rows) */
     CB_T_KMEANS = 6,
+    CB_T_RANSAC_WAVES = 7, /* work counter only: scoring launches that found hypotheses below the budget */
     CB_TIMING_CLASSES = 8
 };
+/* bytes of host<->device copies the library itself has issued on this context since cb_create (the
+ * staging of cb_sym_pose: seed rows and k-means++ draws up, segment offsets and poses back) */
+int cb_copy_bytes(const cb_ctx* ctx, int64_t* h2d, int64_t* d2h);
 int cb_timing_enable(cb_ctx* ctx, int on);
 int cb_timing_read(cb_ctx* ctx, int cls, double* ms, double* work, int64_t* launches);
 int cb_timing_reset(cb_ctx* ctx);
@@ -290,6 +297,35 @@ int cb_sym_pose(cb_ctx* ctx, const float* base_f, const float* base_xyz, int n0,
                 const int32_t* h_samples_pos, int n_samples, int64_t np_seed, int n_nn, const int32_t* h_km_first,
                 const double* h_km_unif, int n_init, int n_trials, double min_center, double max_dist,
                 uint64_t seed, int h_total, int adaptive, double confidence, double* h_out, void* stream);
+
+/* ---- the registration loop of evaluation.py:297-313 in one call ----------------------------------
+ * One record per query-CAD pair: the arguments of cb_sym_pose (device pointers first, host pointers
+ * where that call takes host pointers; every pair brings its own k-means++ draws because they depend
+ * on n_nn = min(50, n0, n1) and K). */
+typedef struct cb_sym_job {
+    const float* base_f;    /* device [n0, d] */
+    const float* base_xyz;  /* device [n0, 3] */
+    const float* pos_f;     /* device [n1, d] */
+    const float* pos_xyz;   /* device [n1, 3] */
+    int32_t n0, n1, d, pos_sym, k_nn, n_samples, n_nn, n_init, n_trials, h_total, adaptive, reserved;
+    int64_t np_seed;
+    const int32_t* h_samples_base; /* host, or NULL with np_seed >= 0 */
+    const int32_t* h_samples_pos;
+    const int32_t* h_km_first;     /* host [n_init] */
+    const double* h_km_unif;       /* host [n_init, K-1, n_trials] */
+    double min_center, max_dist, confidence;
+    uint64_t seed;
+    double* h_out;                 /* host [40], as cb_sym_pose */
+} cb_sym_job;
+/* Registers n_jobs independent pairs with up to `concurrency` of them in flight (each on its own
+ * internal stream set), driven by the calling thread alone: it enqueues a pair's next stage when the
+ * event of the previous one has completed and never sleeps in the driver while another pair has work
+ * to enqueue.  The inputs must be complete on `stream`; on return every h_out is on the host.
+ * Results are those of n_jobs cb_sym_pose calls.  h_status [n_jobs] (may be NULL) receives each
+ * pair's status; the first failure stops new pairs from starting and is returned.  concurrency <= 1
+ * (or timing enabled) runs the pairs one after the other on `stream`. */
+int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs, int concurrency, int32_t* h_status,
+                     void* stream);
 
 /* ---- K5: IRLS pose (utils/_transform_estimation.py:110-137) ------------------------------
  * est_quad_linear_robust: iters (reference: 20) iterations of the linearised weighted solve.

@@ -37,13 +37,26 @@ def find_knn_exact(feat0, feat1, k):
     idx = np.empty((len(f0), k), np.int64)
     d2o = np.empty((len(f0), k), np.float64)
     step = max(1, (1 << 24) // max(1, len(f1)))
+    n1 = len(f1)
+    kk = min(n1, k + 8)
     for s in range(0, len(f0), step):
         blk = f0[s:s + step]
-        d2 = np.zeros((len(blk), len(f1)))
+        d2 = np.zeros((len(blk), n1))
         for c in range(f0.shape[1]):
             df = blk[:, c:c + 1] - f1[None, :, c]
             d2 += df * df
-        order = np.lexsort((np.broadcast_to(np.arange(len(f1)), d2.shape), d2), axis=1)[:, :k]
+        if kk < n1 and n1 > 4096:
+            # large problems: order only the kk smallest of every row, and fall back to the full
+            # ordering for rows whose k-th value ties with the cut (same result, far less sorting)
+            part = np.argpartition(d2, kk - 1, axis=1)[:, :kk]
+            pv = np.take_along_axis(d2, part, 1)
+            o = np.lexsort((part, pv), axis=1)
+            part, pv = np.take_along_axis(part, o, 1), np.take_along_axis(pv, o, 1)
+            order = part[:, :k]
+            for row in np.nonzero(pv[:, k - 1] >= pv[:, kk - 1])[0]:
+                order[row] = np.lexsort((np.arange(n1), d2[row]))[:k]
+        else:
+            order = np.lexsort((np.broadcast_to(np.arange(n1), d2.shape), d2), axis=1)[:, :k]
         idx[s:s + step] = order
         d2o[s:s + step] = np.take_along_axis(d2, order, 1)
     return idx, d2o

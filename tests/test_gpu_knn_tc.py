@@ -28,3 +28,31 @@ def test_knn_tc_exact_and_no_fallback(ctx, rng, d, n0, n1, k):
     np.testing.assert_allclose(dist.cpu().numpy(), ref_d2, rtol=1e-6, atol=1e-12)
     # the split-bf16 candidate scores are accurate to ~1e-5: only genuine near-ties may fall back
     assert 0 <= fb <= max(2, n0 // 200), f"{fb} of {n0} rows needed the exact fallback"
+
+
+@pytest.mark.parametrize("d", [16, 32])
+@pytest.mark.parametrize("k", [1, 5, 50])
+def test_knn_quoted_shape_50000_x_10000(ctx, d, k):
+    """SURVEY.md 8(c)(i) at the shape bench.py quotes `knn_tensor` on (BASELINE.json configs[4]: a
+    50 000-point scan against a 10 000-point CAD) vs utils/find_nn.py:43-49 restated in float64.  The
+    device answers all 50 000 rows; the oracle checks a seeded sample of 2 048 of them (the float64
+    difference-form rows of all 50 000 would take minutes in NumPy) plus the first and last rows."""
+    import torch
+    from corsair_b200 import find_nn
+    rng = np.random.default_rng(1000 + 10 * d + k)
+    F0, F1 = unit_features(rng, 50000, d, clusters=40), unit_features(rng, 10000, d, clusters=40)
+    idx, dist = find_nn.knn_device(F0, F1, k, return_distance=True)
+    fb = ctx.knn_last_fallback_rows() if k <= 12 else 0
+    rows = np.unique(np.concatenate([rng.choice(50000, 2048, replace=False), [0, 49999]]))
+    ref_idx, ref_d2 = port.find_knn_exact(F0[rows], F1, k)
+    got_idx, got_d = idx.cpu().numpy()[rows], dist.cpu().numpy()[rows]
+    assert np.array_equal(got_idx, ref_idx)
+    np.testing.assert_allclose(got_d, ref_d2, rtol=1e-6, atol=1e-12)
+    # every row of the answer is a sorted list of distinct, valid reference ids
+    full = idx.cpu().numpy()
+    assert full.min() >= 0 and full.max() < 10000
+    if k > 1:
+        assert (np.diff(dist.cpu().numpy(), axis=1) >= 0).all()
+        assert (np.sort(full, axis=1)[:, 1:] != np.sort(full, axis=1)[:, :-1]).all()
+    # k <= 12 runs the tensor-core candidate pass: only genuine near-ties may need the exact fallback
+    assert 0 <= fb <= 50000 // 200, f"{fb} of 50000 rows needed the exact fallback"

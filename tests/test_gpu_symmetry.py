@@ -188,20 +188,40 @@ def test_irls_pose(ctx, rng):
 
 
 def test_sym_pose_many_matches_sequential(ctx):
-    """The threaded driver (own context + stream per host thread) returns exactly what the
-    sequential loop returns, in job order."""
+    """cb_sym_pose_many (one host thread, several pairs in flight on internal streams) returns exactly
+    what one cb_sym_pose call per pair returns, in job order, whatever the concurrency; a chair
+    (three registrations) and a table (nine) are mixed so that the longest-first reordering is used."""
     from corsair_b200 import symmetry, synth
-    pairs = [synth.make_pair(200 + i, 32, "chair", n_raw=3000) for i in range(5)]
+    pairs = [synth.make_pair(200 + i, 32, "table" if i == 2 else "chair", n_raw=3000) for i in range(5)]
     def jobs():
         return [((p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"]),
-                 dict(k_nn=5, max_corr=0.2, seed=3, rng=np.random.RandomState(3), n_hypotheses=20000)) for p in pairs]
+                 dict(k_nn=5, max_corr=0.2, seed=3, rng=3 + i, n_hypotheses=20000)) for i, p in enumerate(pairs)]
+    one = [symmetry.sym_pose(*a, **k) for a, k in jobs()]
     seq = symmetry.sym_pose_many(jobs(), workers=1)
     par = symmetry.sym_pose_many(jobs(), workers=3)
-    par2 = symmetry.sym_pose_many(jobs(), workers=3)
-    for a, b, c in zip(seq, par, par2):
-        for x in (b, c):
+    par2 = symmetry.sym_pose_many(jobs(), workers=8)
+    assert len({id(r) for r in par}) == len(pairs)
+    for a, b, c, d in zip(one, seq, par, par2):
+        for x in (b, c, d):
             assert np.array_equal(a[0].numpy(), x[0].numpy()) and np.array_equal(a[2].numpy(), x[2].numpy())
             assert a[1] == x[1] and a[3] == x[3] and a[4] == x[4]
+    # positional k_nn / max_corr / seed (evaluation_registration passes them that way) and a RandomState
+    # (sequential draw order is kept: one pair after the other)
+    pos = symmetry.sym_pose_many([(a + (5, 0.2, 3), dict(rng=k["rng"], n_hypotheses=20000)) for a, k in jobs()], workers=3)
+    rs = symmetry.sym_pose_many([(a, dict(k, rng=np.random.RandomState(k["rng"]))) for a, k in jobs()], workers=3)
+    for a, b, c in zip(one, pos, rs):
+        assert np.array_equal(a[0].numpy(), b[0].numpy()) and a[1] == b[1]
+        assert np.array_equal(a[0].numpy(), c[0].numpy()) and a[1] == c[1]
+
+
+def test_sym_pose_many_reports_a_failing_pair(ctx):
+    """A pair the C call rejects (k_nn above the target cloud's size is caught in Python; here a
+    feature width the engine does not take) surfaces as an exception, not as a silent default."""
+    from corsair_b200 import symmetry, synth
+    p = synth.make_pair(7, 32, "chair", n_raw=2000)
+    bad = ((p["baseF"], p["xyz0"], p["posF"][:3], p["xyz1"][:3], 1), dict(k_nn=5, rng=1))
+    with pytest.raises(ValueError):
+        symmetry.sym_pose_many([bad, bad], workers=2)
 
 
 @pytest.mark.parametrize("category", ["chair", "table"])
