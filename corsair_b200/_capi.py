@@ -134,6 +134,7 @@ class Context:
         if rc != 0 or not h:
             raise RuntimeError(f"cb_create failed with status {rc}")
         self.handle = h
+        self._last_stream = None
         self.h2d_bytes = 0  # counted where the copies are made: dev() / host()
         self.d2h_bytes = 0
 
@@ -150,7 +151,18 @@ class Context:
 
     @property
     def stream(self):
-        return c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        """torch's current stream on this device.  The cb_ctx arena is rewound by every public call and
+        is only safe for one stream at a time: when the caller has switched streams since the last call
+        (``with torch.cuda.stream(s2):``), the new stream is made to wait for the work the old one still
+        has in flight before it may overwrite that scratch."""
+        cur = torch.cuda.current_stream(self.device)
+        last = self._last_stream
+        if last is not None and last.cuda_stream != cur.cuda_stream:
+            ev = torch.cuda.Event()
+            ev.record(last)
+            cur.wait_event(ev)
+        self._last_stream = cur
+        return c_void_p(cur.cuda_stream)
 
     def call(self, name, *args):
         rc = getattr(self.lib, name)(self.handle, *args)

@@ -128,6 +128,26 @@ __device__ __forceinline__ double knn_exact_key(const float* __restrict__ qp, co
     return acc;
 }
 
+// the same operations with the query row already converted (exact) and a compile-time width
+template <int D>
+__device__ __forceinline__ double knn_exact_key_q64(const double* __restrict__ qd, const float* __restrict__ rp, int d,
+                                                    int maxdot) {
+    double acc = 0.0;
+    if (maxdot) {
+#pragma unroll
+        for (int c = 0; c < (D ? D : 32); ++c)
+            if (D || c < d) acc = __dadd_rn(acc, __dmul_rn(qd[c], (double)rp[c]));
+        return -acc;
+    }
+#pragma unroll
+    for (int c = 0; c < (D ? D : 32); ++c)
+        if (D || c < d) {
+            const double df = __dsub_rn(qd[c], (double)rp[c]);
+            acc = __dadd_rn(acc, __dmul_rn(df, df));
+        }
+    return acc;
+}
+
 __device__ __forceinline__ bool knn_less(double a, int ia, double b, int ib) {
     return a < b || (a == b && ia < ib);
 }
@@ -148,9 +168,26 @@ __device__ __forceinline__ double knn_unsortable(unsigned long long s) {
     return __longlong_as_double((long long)((s >> 63) ? (s & 0x7fffffffffffffffull) : ~s));
 }
 
+constexpr int kRowPad = 33;  // floats per staged row: lane l reading column c of row l hits bank (l + c) % 32
+
+// asynchronous 4-byte copy global -> shared (LDGSTS): the copies of a whole batch are in flight together;
+// with a register in between ptxas paired every load with its store and the rows arrived one L2
+// latency after the other (SASS, round 2)
+__device__ __forceinline__ void knn_cp_async4(float* dst_smem, const float* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void knn_cp_async_wait() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
 // one warp per query; ncand = S*KC <= 32*SL candidate slots (SL per lane; unused slots hold -1).
 // bound (optional, [nq, S]): per chunk a score no dropped reference of that chunk is below;
 // without it the chunk's last (worst kept) candidate score plays that role.
+// Candidate rows are gathered COOPERATIVELY: the warp copies each candidate's row with one coalesced
+// load into shared memory and every lane then walks its own row there (round 1: every lane walked its
+// own global row with scalar loads, 32 cache lines per load instruction — the kernel was bound by L1
+// tag traffic, 322 us at 50 000 x 10 000 with ~48 candidates per query).
 // The k rounds of "smallest remaining (key, index)" are three warp-wide integer minima (REDUX) each:
 // high word of the key, low word among the lanes that match, index among those that still match.
 template <int SL>
@@ -158,28 +195,43 @@ __global__ void __launch_bounds__(256)
 knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int d, int dq_stride,
                   int k, int metric, const int32_t* __restrict__ cand_idx, const float* __restrict__ cand_s,
                   int S, int KC, const float* __restrict__ bound, const unsigned int* __restrict__ rmax_bits,
-                  double gamma,
+                  double gamma, const int32_t* __restrict__ unscramble,
                   int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist,
                   int32_t* __restrict__ fb_list, int* __restrict__ fb_count) {
-    const int lane = threadIdx.x & 31;
-    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    __shared__ float s_rows[8][32][kRowPad];
+    __shared__ double s_q[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int qi = blockIdx.x * (blockDim.x >> 5) + warp;
     if (qi >= nq) return;
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int ncand = S * KC;
     const float* qp = q + (size_t)qi * dq_stride;
+    float (*rows)[kRowPad] = s_rows[warp];
+    s_q[warp][lane] = lane < d ? (double)qp[lane] : 0.0;
     unsigned long long key[SL];
     int id[SL];
 #pragma unroll
     for (int t = 0; t < SL; ++t) {
-        int ci = lane + 32 * t;
+        const int ci = lane + 32 * t;
+        int j = ci < ncand ? cand_idx[(size_t)qi * ncand + ci] : -1;
+        if (unscramble && j >= 0) j = unscramble[j];
         id[t] = 0x7fffffff;
         key[t] = ~0ull;
-        if (ci < ncand) {
-            int j = cand_idx[(size_t)qi * ncand + ci];
-            if (j >= 0) {
-                id[t] = j;
-                key[t] = knn_sortable(knn_exact_key(qp, r + (size_t)j * dq_stride, d, maxdot));
-            }
+        if (!__ballot_sync(0xffffffffu, j >= 0)) continue;
+        __syncwarp();
+#pragma unroll 8
+        for (int rr = 0; rr < 32; ++rr) {
+            const int jj = __shfl_sync(0xffffffffu, j, rr);
+            if (jj >= 0 && lane < d) knn_cp_async4(&rows[rr][lane], r + (size_t)jj * dq_stride + lane);
+        }
+        knn_cp_async_wait();
+        __syncwarp();
+        if (j >= 0) {
+            id[t] = j;
+            const double kd = d == 32 ? knn_exact_key_q64<32>(s_q[warp], rows[lane], d, maxdot)
+                                      : (d == 16 ? knn_exact_key_q64<16>(s_q[warp], rows[lane], d, maxdot)
+                                                 : knn_exact_key_q64<0>(s_q[warp], rows[lane], d, maxdot));
+            key[t] = knn_sortable(kd);
         }
     }
     double kth = 0.0;
@@ -233,52 +285,90 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
     if (bad && lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
 }
 
-// exact float64 brute force for the queued rows: one block per row, k rounds of
-// "smallest (key,index) above the previous one"
+// exact float64 brute force for the queued rows: one block per row.  The block stages 256 references
+// at a time in shared memory with coalesced loads; every thread evaluates one of them per tile and
+// keeps its own k best in registers (sorted, k <= 12 in engine E1); the block then merges the 256
+// sorted lists in k rounds of "smallest head".  (Round 1 rescanned all references once per round, every
+// thread walking its own global rows: 900 us for a single queued row at 50 000 x 10 000.)
+constexpr int kFbK = 12;
 __global__ void __launch_bounds__(256)
 knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, int nr, int d, int stride,
                     int k, int metric, const int32_t* __restrict__ fb_list, const int* __restrict__ fb_count,
                     int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist) {
-    __shared__ double wk[8];
-    __shared__ int wj[8];
-    __shared__ double prev_k;
-    __shared__ int prev_j;
+    __shared__ float s_rows[256][kRowPad];
+    __shared__ float s_q[32];
+    __shared__ unsigned long long s_key[8];
+    __shared__ int s_id[8];
+    __shared__ unsigned long long s_wkey;
+    __shared__ int s_wid;
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int n = *fb_count;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int e = blockIdx.x; e < n; e += gridDim.x) {
         const int qi = fb_list[e];
-        const float* qp = q + (size_t)qi * stride;
-        if (threadIdx.x == 0) { prev_k = -INFINITY; prev_j = -1; }
         __syncthreads();
+        if (threadIdx.x < 32) s_q[threadIdx.x] = threadIdx.x < d ? q[(size_t)qi * stride + threadIdx.x] : 0.f;
+        unsigned long long bk[kFbK];
+        int bj[kFbK];
+#pragma unroll
+        for (int t = 0; t < kFbK; ++t) { bk[t] = ~0ull; bj[t] = 0x7fffffff; }
+        for (int base = 0; base < nr; base += 256) {
+            const int nt = min(256, nr - base);
+            __syncthreads();
+            // warp w copies rows w, w + 8, ...: one coalesced load per row
+            if (lane < d)
+                for (int rr = warp; rr < nt; rr += 8) knn_cp_async4(&s_rows[rr][lane], r + (size_t)(base + rr) * stride + lane);
+            knn_cp_async_wait();
+            __syncthreads();
+            if ((int)threadIdx.x < nt) {
+                const unsigned long long key = knn_sortable(knn_exact_key(s_q, s_rows[threadIdx.x], d, maxdot));
+                const int j = base + threadIdx.x;
+                // sorted insertion by (key, index); slots beyond k are never read
+                if (key < bk[kFbK - 1] || (key == bk[kFbK - 1] && j < bj[kFbK - 1])) {
+                    bk[kFbK - 1] = key;
+                    bj[kFbK - 1] = j;
+#pragma unroll
+                    for (int t = kFbK - 1; t > 0; --t) {
+                        const bool sw = bk[t] < bk[t - 1] || (bk[t] == bk[t - 1] && bj[t] < bj[t - 1]);
+                        if (sw) {
+                            const unsigned long long tk = bk[t]; bk[t] = bk[t - 1]; bk[t - 1] = tk;
+                            const int tj = bj[t]; bj[t] = bj[t - 1]; bj[t - 1] = tj;
+                        }
+                    }
+                }
+            }
+        }
         for (int round = 0; round < k; ++round) {
-            const double pk = prev_k;
-            const int pj = prev_j;
-            double bk = INFINITY;
-            int bj = 0x7fffffff;
-            for (int j = threadIdx.x; j < nr; j += blockDim.x) {
-                double key = knn_exact_key(qp, r + (size_t)j * stride, d, maxdot);
-                if (knn_less(pk, pj, key, j) && knn_less(key, j, bk, bj)) { bk = key; bj = j; }
-            }
-            for (int o = 16; o > 0; o >>= 1) {
-                double ok = __shfl_xor_sync(0xffffffffu, bk, o);
-                int oj = __shfl_xor_sync(0xffffffffu, bj, o);
-                if (knn_less(ok, oj, bk, bj)) { bk = ok; bj = oj; }
-            }
-            if ((threadIdx.x & 31) == 0) { wk[threadIdx.x >> 5] = bk; wj[threadIdx.x >> 5] = bj; }
+            // smallest head of the block: warp minima (three REDUX), then the eight warps through shared memory
+            const unsigned hi = (unsigned)(bk[0] >> 32), lo = (unsigned)bk[0];
+            const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+            const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+            const bool tied = hi == mh && lo == ml;
+            const int wj = (int)__reduce_min_sync(0xffffffffu, tied ? (unsigned)bj[0] : 0x7fffffffu);
+            if (lane == 0) { s_key[warp] = ((unsigned long long)mh << 32) | ml; s_id[warp] = wj; }
             __syncthreads();
             if (threadIdx.x == 0) {
-                for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
-                    if (knn_less(wk[w], wj[w], bk, bj)) { bk = wk[w]; bj = wj[w]; }
-                size_t o = (size_t)qi * k + round;
-                if (bj != 0x7fffffff) {
-                    if (idx64) idx64[o] = bj;
-                    if (idx32) idx32[o] = bj;
-                    if (dist) dist[o] = knn_out_dist(bk, metric);
+                unsigned long long wk = s_key[0];
+                int wi = s_id[0];
+                for (int w = 1; w < 8; ++w)
+                    if (s_key[w] < wk || (s_key[w] == wk && s_id[w] < wi)) { wk = s_key[w]; wi = s_id[w]; }
+                s_wkey = wk;
+                s_wid = wi;
+                if (wi != 0x7fffffff) {
+                    const size_t o = (size_t)qi * k + round;
+                    if (idx64) idx64[o] = wi;
+                    if (idx32) idx32[o] = wi;
+                    if (dist) dist[o] = knn_out_dist(knn_unsortable(wk), metric);
                 }
-                prev_k = bk;
-                prev_j = bj;
             }
             __syncthreads();
+            if (bj[0] == s_wid && bk[0] == s_wkey) {
+                // the winner pops its head
+#pragma unroll
+                for (int t = 0; t + 1 < kFbK; ++t) { bk[t] = bk[t + 1]; bj[t] = bj[t + 1]; }
+                bk[kFbK - 1] = ~0ull;
+                bj[kFbK - 1] = 0x7fffffff;
+            }
         }
     }
 }
@@ -312,7 +402,7 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     const int dp = d <= 16 ? 16 : 32;
     const int KC = k <= 5 ? 8 : 16;
     // the tcgen05 variant collects every reference at or above a per-(query, chunk) threshold: up to
-    // LC = 5 KC list slots per chunk; the SIMT variant keeps exactly the KC best
+    // LC = 6 KC list slots per chunk; the SIMT variant keeps exactly the KC best
     const bool use_tc = ctx->knn_variant != 1;
     const int LC = use_tc ? knn_cand_tc_list_slots(KC) : KC;
     const int qblocks = cb_div_up(nq, 128);
@@ -328,7 +418,8 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
             const int tps = cb_div_up(tiles, s_try);
             const int ss = cb_div_up(tiles, tps);
             const int rounds = cb_div_up(qblocks * ss, ctx->sm_count);
-            const double cost = rounds * (knn_cand_tc_passes(tps) + 1.5);
+            // every extra chunk adds ~2 KC candidates per query to append and re-rank: 3 % per chunk
+            const double cost = rounds * (knn_cand_tc_passes(tps) + 1.5) * (1.0 + 0.03 * ss);
             if (cost < best_cost - 1e-9) { best_cost = cost; best_tps = tps; }
         }
         chunk = best_tps * 256;
@@ -357,9 +448,10 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     const float* rd = r;
     int stride = d;
     float* cs = nullptr;
+    const int32_t* unscramble = nullptr;
     if (use_tc) {
         cb_timed_scope tscope(ctx, CB_T_KNN_CAND, 2.0 * nq * (double)nr * dp, st);
-        int rc = knn_cand_tc_launch(ctx, q, nq, r, nr, d, dp, KC, LC, chunk, S, maxdot, ci, bound, scal, st);
+        int rc = knn_cand_tc_launch(ctx, q, nq, r, nr, d, dp, KC, LC, chunk, S, maxdot, ci, bound, scal, &unscramble, st);
         if (rc) return rc;
         gamma = knn_cand_tc_gamma(dp);
     } else {
@@ -393,7 +485,7 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
         auto kern = SL <= 1 ? knn_rerank_kernel<1> : SL <= 2 ? knn_rerank_kernel<2> : SL <= 4 ? knn_rerank_kernel<4>
                                                                                                : knn_rerank_kernel<8>;
         kern<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, stride, k, metric, ci, cs, S, LC, use_tc ? bound : nullptr,
-                                               scal, gamma, idx, idx32, dist, fb, (int*)(scal + 1));
+                                               scal, gamma, unscramble, idx, idx32, dist, fb, (int*)(scal + 1));
         CB_LAUNCH_CHECK(ctx);
     }
     knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, stride, k, metric, fb,
@@ -410,7 +502,7 @@ static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
     b += cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nr * 32 * 4);  // pads
     b += cb_align((size_t)nr * 4) + 256;
     b += 2 * cb_align((size_t)nq * 256 * 4) + cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nq * 4);
-    b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + (1 << 16);  // packed bf16 operand tiles of the tc variant
+    b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + cb_align((size_t)(nr + 256) * 4) + (1 << 16);  // packed bf16 operand tiles + un-scramble table of the tc variant
     return b;
 }
 

@@ -8,14 +8,16 @@
 // SIMT variant: LC = KC, the KC best in ascending order.
 
 // tcgen05 candidate pass (knn_tc.cu), dp in {16,32} (rows of width d <= dp are zero-filled by its packing
-// kernel), KC in {8,16}, LC = 5 KC: every reference of the chunk whose score is at or below the chunk's
+// kernel), KC in {8,16}, LC = 6 KC: every reference of the chunk whose score is at or below the chunk's
 // threshold (the KC-th best of the column-group minima of the chunk's first half, so at least KC
 // references qualify), in no particular order; bound[qi*S + c] = that threshold (no dropped reference
 // scores below it), -inf when more than LC qualified (the re-rank then sends the row to the exact
 // fallback).  *rmax_bits (zeroed by the caller) receives the largest |r|^2 as fp32 bits.
+// cand_idx holds columns of the (row-scrambled) score matrix; *unscramble_out [nr padded to 256] maps a
+// column to its reference index (the re-rank applies it).
 int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int dp, int KC, int LC,
                        int chunk, int S, int maxdot, int32_t* cand_idx, float* bound, unsigned int* rmax_bits,
-                       cudaStream_t st);
+                       const int32_t** unscramble_out, cudaStream_t st);
 int knn_cand_tc_list_slots(int KC);
 // tile passes (MMA + drain of one 128 x 256 accumulator) one CTA of a `tiles`-tile chunk runs
 int knn_cand_tc_passes(int tiles);

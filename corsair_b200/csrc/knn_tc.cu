@@ -28,7 +28,7 @@
 //              list: a packed subtract + funnel shift per column builds a 32-bit qualification
 //              mask per tcgen05.ld, then one short loop over its set bits.
 // Round 1 ran the threshold pass over ALL tiles (every score left tensor memory twice); a threshold
-// from half of the chunk lets ~2 KC references qualify instead of ~KC (list slots: 5 KC) and cuts
+// from half of the chunk lets ~2 KC references qualify instead of ~KC (list slots: 6 KC) and cuts
 // MMA + drain work from 2 T to 1.5 T tile passes.
 #include "common.cuh"
 #include "knn_internal.cuh"
@@ -80,7 +80,8 @@ template <int D>
 __global__ void __launch_bounds__(128)
 knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float* __restrict__ r, int nr, int nr_pad,
                    int d, int maxdot, unsigned perm_a, __nv_bfloat16* __restrict__ Apack,
-                   __nv_bfloat16* __restrict__ Bpack, unsigned int* __restrict__ rmax_bits) {
+                   __nv_bfloat16* __restrict__ Bpack, int32_t* __restrict__ unscramble,
+                   unsigned int* __restrict__ rmax_bits) {
     constexpr int KP = kprime(D);
     const int gid = blockIdx.x * blockDim.x + threadIdx.x;
     const bool is_b = gid >= nq_pad;
@@ -131,6 +132,7 @@ knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float*
         }
         const int TR = is_b ? kTileN : kTileM;
         const int prow = is_b ? (int)(((unsigned long long)row * perm_a) % (unsigned)nr_pad) : row;
+        if (is_b) unscramble[prow] = row < n ? row : -1;  // column of the score matrix -> reference index
         const int tile = prow / TR, rr = prow % TR;
         char* base = reinterpret_cast<char*>(is_b ? Bpack : Apack) + (size_t)tile * TR * KP * 2 +
                      (size_t)(rr >> 3) * 128 + (size_t)(rr & 7) * 16;
@@ -160,25 +162,28 @@ knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float*
 }
 
 struct TcSmemCtl {
-    uint64_t a_full, full[2], empty[2], tmem_full[2], tmem_empty[2];
+    uint64_t a_full, full[4], empty[4], tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
 };
 
-template <int D, int KC>
+// NB = shared-memory stages of B tiles.  The tile of step it + NB - 1 is requested when the MMAs of step
+// it - 1 have completed; a 56 KB bulk copy from L2 takes longer than the 7 MMAs of one step, so two
+// stages (round 1) left the tensor pipe waiting for operands.
+template <int D, int KC, int NB>
 __global__ void __launch_bounds__(kThreads, 1)
 knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack, int nq, int nr,
-              int chunk, int S, int maxdot, unsigned perm_inv, int nr_pad, int32_t* __restrict__ cand_idx,
-              float* __restrict__ bound) {
+              int chunk, int S, int maxdot, int32_t* __restrict__ cand_idx, float* __restrict__ bound) {
     constexpr int KP = kprime(D);
-    constexpr int LC = 5 * KC;            // list slots per (query, chunk): P(overflow) ~ 2e-5
-    constexpr int GROUP = 128 / KC;       // columns per group maximum: 16 (KC = 8) or 8 (KC = 16)
+    constexpr int LC = 6 * KC;            // list slots per (query, chunk): P(overflow) ~ 3e-7
+    constexpr int GROUP = 8;              // columns per group maximum (16 let 4 % of the rows of clustered
+                                          // features overflow their list in two-tile chunks, 8: < 0.1 %)
     constexpr uint32_t A_BYTES = kTileM * KP * 2, B_BYTES = kTileN * KP * 2;
     constexpr uint32_t LBO_A = (kTileM / 8) * 128, LBO_B = (kTileN / 8) * 128;
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* sA = smem;
     unsigned char* sB = smem + A_BYTES;
-    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + 2 * B_BYTES);
-    float* s_top = reinterpret_cast<float*>(smem + A_BYTES + 2 * B_BYTES + 128);  // [kColParts][kTileM][KC]
+    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + NB * B_BYTES);
+    float* s_top = reinterpret_cast<float*>(smem + A_BYTES + NB * B_BYTES + 128);  // [kColParts][kTileM][KC]
     int* s_cnt = reinterpret_cast<int*>(s_top + kColParts * kTileM * KC);        // [kTileM]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c = blockIdx.y;
@@ -190,9 +195,11 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
 
     if (threadIdx.x == 0) {
         tc::mbar_init(&ctl->a_full, 1);
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < NB; ++i) {
             tc::mbar_init(&ctl->full[i], 1);
             tc::mbar_init(&ctl->empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
             tc::mbar_init(&ctl->tmem_full[i], 1);
             tc::mbar_init(&ctl->tmem_empty[i], kEpiWarps);
         }
@@ -211,7 +218,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             tc::mbar_arrive_expect_tx(&ctl->a_full, A_BYTES);
             tc::bulk_g2s(sA, reinterpret_cast<const char*>(Apack) + (size_t)blockIdx.x * A_BYTES, A_BYTES, &ctl->a_full);
             for (int it = 0; it < nsteps; ++it) {
-                const int st = it & 1, use = it >> 1;
+                const int st = it % NB, use = it / NB;
                 const int tile = t0 + (it >= nthr ? it - nthr : it);
                 tc::mbar_wait(&ctl->empty[st], (use & 1) ^ 1);
                 tc::mbar_arrive_expect_tx(&ctl->full[st], B_BYTES);
@@ -226,19 +233,20 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             const uint32_t a_addr = tc::smem_u32(sA);
             tc::mbar_wait(&ctl->a_full, 0);
             for (int it = 0; it < nsteps; ++it) {
-                const int st = it & 1, use = it >> 1;
+                const int st = it % NB, use = it / NB;   // shared-memory stage
+                const int ts = it & 1, tuse = it >> 1;   // tensor-memory stage
                 tc::mbar_wait(&ctl->full[st], use & 1);
-                tc::mbar_wait(&ctl->tmem_empty[st], (use & 1) ^ 1);
+                tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
                 tc::fence_after_sync();
                 const uint32_t b_addr = tc::smem_u32(sB + st * B_BYTES);
 #pragma unroll
                 for (int ks = 0; ks < KP / 16; ++ks) {
                     const uint64_t ad = tc::smem_desc(a_addr + ks * 2 * LBO_A, LBO_A, 128);
                     const uint64_t bd = tc::smem_desc(b_addr + ks * 2 * LBO_B, LBO_B, 128);
-                    tc::mma_bf16(tbase + st * kTileN, ad, bd, idesc, ks > 0);
+                    tc::mma_bf16(tbase + ts * kTileN, ad, bd, idesc, ks > 0);
                 }
                 tc::mma_commit(&ctl->empty[st]);      // smem stage reusable once these MMAs finish
-                tc::mma_commit(&ctl->tmem_full[st]);  // accumulator ready for the epilogue
+                tc::mma_commit(&ctl->tmem_full[ts]);  // accumulator ready for the epilogue
             }
         }
     } else {
@@ -249,7 +257,11 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
         const size_t o = ((size_t)min(qi, nq - 1) * S + c) * LC;
         const bool live = qi < nq;
         const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + part * kPartN;
-        float top[KC];  // the KC best group maxima of this thread's columns, descending
+        // the KT = KC / 2 best group maxima of this thread's columns, descending.  The row's threshold is the
+        // KC-th best of the four threads' lists: a thread that holds more than KT of the row's KC best
+        // group maxima (11 % of the rows) lowers it slightly, which only lets a few more references qualify
+        constexpr int KT = KC / 2;
+        float top[KC];
 #pragma unroll
         for (int t = 0; t < KC; ++t) top[t] = -INFINITY;
         float tau = -INFINITY;
@@ -260,13 +272,13 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             if (it == nthr) {
                 // the row's threshold: KC-th best of the union of its four threads' group maxima
 #pragma unroll
-                for (int t = 0; t < KC; ++t) s_top[(part * kTileM + row) * KC + t] = top[t];
+                for (int t = 0; t < KT; ++t) s_top[(part * kTileM + row) * KC + t] = top[t];
                 named_bar_sync(1, kEpiThreads);
 #pragma unroll
                 for (int p = 1; p < kColParts; ++p) {
                     const float* other = s_top + (((part + p) % kColParts) * kTileM + row) * KC;
 #pragma unroll
-                    for (int u = 0; u < KC; ++u) {
+                    for (int u = 0; u < KT; ++u) {
                         float x = other[u];
 #pragma unroll
                         for (int t = 0; t < KC; ++t) {
@@ -294,18 +306,15 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             if (!collect) {
 #pragma unroll
                 for (int g = 0; g < kPartN / GROUP; ++g) {
-                    // group maximum as a tree (FMNMX3 in SASS), then a branch-free insertion into the
+                    // group maximum by three-input maxima (FMNMX3), then a branch-free insertion into the
                     // descending list (x sinks to its place)
-                    float m[GROUP];
+                    const float* m = v + g * GROUP;
+                    static_assert(GROUP == 8, "the maximum tree below is written for groups of 8");
+                    const float a0 = fmaxf(fmaxf(m[0], m[1]), m[2]);
+                    const float a1 = fmaxf(fmaxf(m[3], m[4]), m[5]);
+                    float x = fmaxf(fmaxf(a0, a1), fmaxf(m[6], m[7]));
 #pragma unroll
-                    for (int e = 0; e < GROUP; ++e) m[e] = v[g * GROUP + e];
-#pragma unroll
-                    for (int w = GROUP / 2; w > 0; w >>= 1)
-#pragma unroll
-                        for (int e = 0; e < w; ++e) m[e] = fmaxf(m[e], m[e + w]);
-                    float x = m[0];
-#pragma unroll
-                    for (int t = 0; t < KC; ++t) {
+                    for (int t = 0; t < KT; ++t) {
                         const float hi = fmaxf(top[t], x);
                         x = fminf(top[t], x);
                         top[t] = hi;
@@ -317,14 +326,17 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                     // which of the 32 columns qualify: packed v - tau (two columns per instruction), the
                     // sign bit (set: below the threshold) shifted into the word by one funnel shift;
                     // column e lands at bit 31 - e, hence the bit reversal
-                    unsigned below = 0;
+                    // (four independent 8-column chains: one 32-long chain of dependent shifts left the
+                    // ALU pipe waiting on its own latency)
+                    unsigned b4[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
                     for (int e = 0; e < 32; e += 2) {
                         float d0, d1;
                         unpk2(add2(pk2(v[h * 32 + e], v[h * 32 + e + 1]), ntau2), d0, d1);
-                        below = __funnelshift_l(__float_as_uint(d0), below, 1);
-                        below = __funnelshift_l(__float_as_uint(d1), below, 1);
+                        b4[e >> 3] = __funnelshift_l(__float_as_uint(d0), b4[e >> 3], 1);
+                        b4[e >> 3] = __funnelshift_l(__float_as_uint(d1), b4[e >> 3], 1);
                     }
+                    const unsigned below = (b4[0] << 24) | (b4[1] << 16) | (b4[2] << 8) | b4[3];
                     unsigned mask = __brev(~below);
                     // padding rows (all-equal scores) and rows whose list already overflowed (they go
                     // to the exact fallback whatever else qualifies) must not spin in the loop below
@@ -335,8 +347,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                         const int e = __ffs(mask) - 1;
                         mask &= mask - 1;
                         const int pos = atomicAdd(&s_cnt[row], 1);
-                        if (pos < LC)
-                            cand_idx[o + pos] = (int)(((unsigned long long)(col0 + h * 32 + e) * perm_inv) % (unsigned)nr_pad);
+                        if (pos < LC) cand_idx[o + pos] = col0 + h * 32 + e;  // scrambled column: the re-rank maps it back
                     }
                 }
             }
@@ -355,14 +366,24 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
 }
 
 template <int D, int KC>
+constexpr int b_stages() {
+    // as many 256-row B stages as fit beside the A tile and the threshold lists (227 KB per CTA)
+    return (227 * 1024 - kTileM * kprime(D) * 2 - 128 - kColParts * kTileM * KC * 4 - kTileM * 4 - 64) / (kTileN * kprime(D) * 2) >= 4
+               ? 4
+               : (227 * 1024 - kTileM * kprime(D) * 2 - 128 - kColParts * kTileM * KC * 4 - kTileM * 4 - 64) / (kTileN * kprime(D) * 2);
+}
+
+template <int D, int KC>
 cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
-                      unsigned perm_inv, int nr_pad, int32_t* ci, float* bound, cudaStream_t st) {
+                      int32_t* ci, float* bound, cudaStream_t st) {
     constexpr int KP = kprime(D);
-    const size_t smem = (size_t)kTileM * KP * 2 + 2 * (size_t)kTileN * KP * 2 + 128 + kColParts * kTileM * KC * 4 + kTileM * 4 + 64;
-    cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    constexpr int NB = b_stages<D, KC>();
+    static_assert(NB >= 2, "at least two B stages");
+    const size_t smem = (size_t)kTileM * KP * 2 + NB * (size_t)kTileN * KP * 2 + 128 + kColParts * kTileM * KC * 4 + kTileM * 4 + 64;
+    cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((nq + kTileM - 1) / kTileM, S);
-    knn_tc_kernel<D, KC><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, ci, bound);
+    knn_tc_kernel<D, KC, NB><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, ci, bound);
     return cudaGetLastError();
 }
 
@@ -374,40 +395,44 @@ extern "C" const char* cb_knn_variant(const cb_ctx* ctx) {
     return (ctx && ctx->knn_variant == 1) ? "simt" : "tcgen05";
 }
 
-int knn_cand_tc_list_slots(int KC) { return 5 * KC; }
+int knn_cand_tc_list_slots(int KC) { return 6 * KC; }
 
 // tile passes (MMA + drain of one 128 x 256 accumulator) one CTA of a `tiles`-tile chunk runs
 int knn_cand_tc_passes(int tiles) { return tiles + (tiles + 1) / 2; }
 
-// q [nq, d], r [nr, d] raw rows (d <= dp, dp in {16, 32}); writes *rmax_bits (zeroed by the caller)
+// q [nq, d], r [nr, d] raw rows (d <= dp, dp in {16, 32}); writes *rmax_bits (zeroed by the caller).
+// cand_idx receives COLUMNS of the scrambled score matrix; *unscramble_out [nr_pad] maps them to
+// reference indices (the re-rank applies it).
 int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int d, int dp, int KC, int LC,
                        int chunk, int S, int maxdot, int32_t* cand_idx, float* bound, unsigned int* rmax_bits,
-                       cudaStream_t st) {
-    if ((dp != 16 && dp != 32) || d > dp || (KC != 8 && KC != 16) || LC != 5 * KC || chunk % kTileN != 0)
+                       const int32_t** unscramble_out, cudaStream_t st) {
+    if ((dp != 16 && dp != 32) || d > dp || (KC != 8 && KC != 16) || LC != 6 * KC || chunk % kTileN != 0)
         CB_FAIL(ctx, CB_EUNSUPPORTED, "knn_cand_tc_launch: unsupported shape (d=%d KC=%d LC=%d chunk=%d)", d, KC, LC, chunk);
     const int KP = kprime(dp);
     const int nq_pad = cb_div_up(nq, kTileM) * kTileM, nr_pad = cb_div_up(nr, kTileN) * kTileN;
     __nv_bfloat16* A = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nq_pad * KP);
     __nv_bfloat16* B = cb_alloc_t<__nv_bfloat16>(ctx, (size_t)nr_pad * KP);
-    if (!A || !B) return CB_ENOMEM;
+    int32_t* unscramble = cb_alloc_t<int32_t>(ctx, nr_pad);
+    if (!A || !B || !unscramble) return CB_ENOMEM;
+    *unscramble_out = unscramble;
     // multiplicative scramble of the reference rows: perm_a ~ 0.618 n_pad, coprime to n_pad
-    unsigned perm_a = ((unsigned)(0.6180339887 * nr_pad)) | 1u, perm_inv = 1;
+    unsigned perm_a = ((unsigned)(0.6180339887 * nr_pad)) | 1u;
     for (;; perm_a += 2) {
-        long long g0 = nr_pad, g1 = perm_a % (unsigned)nr_pad, x0 = 0, x1 = 1;  // extended Euclid
-        while (g1) { long long qq = g0 / g1, t = g0 - qq * g1; g0 = g1; g1 = t; t = x0 - qq * x1; x0 = x1; x1 = t; }
-        if (g0 == 1) { perm_inv = (unsigned)((x0 % nr_pad + nr_pad) % nr_pad); perm_a %= (unsigned)nr_pad; break; }
+        unsigned g0 = (unsigned)nr_pad, g1 = perm_a % (unsigned)nr_pad;
+        while (g1) { const unsigned t = g0 % g1; g0 = g1; g1 = t; }
+        if (g0 == 1) { perm_a %= (unsigned)nr_pad; break; }
     }
     const unsigned pack_blocks = (unsigned)cb_div_up(nq_pad + nr_pad, 128);
     if (dp == 16)
-        knn_tc_pack_kernel<16><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, rmax_bits);
+        knn_tc_pack_kernel<16><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, unscramble, rmax_bits);
     else
-        knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, rmax_bits);
+        knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, unscramble, rmax_bits);
     CB_LAUNCH_CHECK(ctx);
     cudaError_t e;
-    if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
-    else if (dp == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
-    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
-    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, perm_inv, nr_pad, cand_idx, bound, st);
+    if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
+    else if (dp == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
+    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
+    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
     ctx->launches++;
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "knn_tc_kernel launch failed: %s", cudaGetErrorString(e));
     return CB_OK;

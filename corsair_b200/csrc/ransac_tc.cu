@@ -29,15 +29,13 @@
 namespace {
 
 constexpr int kHT = 2;            // A tiles (of 128 hypotheses) per CTA
-constexpr int kStages = 3;        // shared-memory ring of B tiles
-constexpr int kEpiWarps = 8;      // 4 lane quadrants x 2 A tiles x kColSplit column parts
-constexpr int kColSplit = kEpiWarps / 8;
-constexpr int kColsPerThread = kRtTileN / kColSplit;
-constexpr int kChunks = kColsPerThread / 32;  // 32-column tcgen05.ld per thread and tile (even)
-constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = kEpiThreads + 64;  // + producer warp + MMA warp
-constexpr int kListCap = 4096;    // queued in-band evaluations per CTA (overflow is settled inline)
-constexpr int kListDrain = 2048;  // drain the queue at the next tile boundary once it holds this many
+constexpr int kStages = 6;        // shared-memory ring of 24 KB B tiles: the copies of five tiles in flight cover the L2 latency
+// epilogue warps: 4 lane quadrants x 2 A tiles x (EW / 8) column parts.  16 (four per SM sub-partition)
+// is the default: with 8 the kernel was bound by the epilogue's dependent-issue latency (ncu, round 2:
+// issue active 48 %, tensor pipe 49 %, warps active 15.6 %, stall `wait` 1.0 per issue)
+constexpr int kMaxEpiWarps = 16;
+constexpr int kListCap = 2048;    // queued in-band evaluations per CTA (overflow is settled inline)
+constexpr int kListDrain = 1024;  // drain the queue at the next tile boundary once it holds this many
 constexpr uint32_t kATileBytes = kRtTileM * kRtKP * 2;  // 24 KB
 constexpr uint32_t kBTileBytes = kRtTileN * kRtKP * 2;  // 24 KB
 
@@ -174,6 +172,7 @@ __device__ __noinline__ void rt_overflow(int col, float u, const double* __restr
 }
 
 // all epilogue threads: re-decide the queued evaluations exactly, corrections into s_dcnt/s_dsum
+template <int kEpiThreads>
 __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s_dcnt, double* s_dsum, int jcta, int w,
                                          const double* __restrict__ Tw, const float4* __restrict__ src4,
                                          const float4* __restrict__ tgt4, double thr2d) {
@@ -188,13 +187,17 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
     }
 }
 
-template <bool DUMP, int LDW, bool WSUM>
-__global__ void __launch_bounds__(kThreads, 1)
+template <bool DUMP, int LDW, bool WSUM, int kEpiWarps>
+__global__ void __launch_bounds__(kEpiWarps * 32 + 64, 1)
 ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
                        const float* __restrict__ band_g, const double* __restrict__ Tw,
                        const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int ntiles_total,
                        int tiles_per_split, int h0, int w, double thr2d, const RansacState* __restrict__ state,
                        int32_t* __restrict__ pc, double* __restrict__ ps, float* __restrict__ dump, int dump_ld) {
+    constexpr int kColSplit = kEpiWarps / 8;
+    constexpr int kColsPerThread = kRtTileN / kColSplit;
+    constexpr int kChunks = kColsPerThread / 32;  // 32-column tcgen05.ld per thread and tile (even)
+    constexpr int kEpiThreads = kEpiWarps * 32;
     // hypotheses at or beyond the (device-side, shrinking) budget are never looked at by the fold
     if (h0 + (int)blockIdx.x * (kHT * kRtTileM) >= state->budget) return;
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -327,7 +330,8 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             }
         };
         constexpr bool kPipelined = LDW == 64 && kChunks == 4;
-        float va[kPipelined ? 64 : 1], vb[kPipelined ? 64 : 1];
+        constexpr bool kBoth = LDW == 64 && kChunks == 2;  // 16 warps: the thread's 64 columns in two loads, one wait
+        float va[kPipelined || kBoth ? 64 : 1], vb[kPipelined ? 64 : 1];
         for (int it = 0; it < ntiles; ++it) {
             const int ts = it & 1, tuse = it >> 1;
             tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
@@ -354,6 +358,17 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                 if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
                 process(*reinterpret_cast<const float(*)[32]>(vb), col0 + 64);
                 process(*reinterpret_cast<const float(*)[32]>(vb + 32), col0 + 96);
+            } else if constexpr (kBoth) {
+                // the stage goes back to the MMA warp as soon as both loads have landed; the arithmetic
+                // overlaps the other three warps of this sub-partition and the next tile's MMAs
+                tc::tmem_ld32(taddr, va);
+                tc::tmem_ld32(taddr + 32, va + 32);
+                tc::tmem_ld_wait64(va);
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
+                process(*reinterpret_cast<const float(*)[32]>(va), col0);
+                process(*reinterpret_cast<const float(*)[32]>(va + 32), col0 + 32);
             } else if constexpr (LDW == 64) {
 #pragma unroll 1
                 for (int k = 0; k < kChunks; k += 2) {
@@ -373,7 +388,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                 }
             }
             // accumulator stage drained: hand it back to the MMA warp
-            if constexpr (!kPipelined) {
+            if constexpr (!kPipelined && !kBoth) {
                 tc::fence_before_sync();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[ts]);
@@ -391,7 +406,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             if ((it & 15) != 15) continue;
             named_bar_sync(1, kEpiThreads);
             if (*(volatile int*)&ctl->list_n >= kListDrain) {
-                rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
+                rt_drain<kEpiThreads>(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
                 named_bar_sync(1, kEpiThreads);
                 if (threadIdx.x == 0) ctl->list_n = 0;
                 named_bar_sync(1, kEpiThreads);
@@ -399,7 +414,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         }
         // settle the queued in-band evaluations of the whole CTA
         named_bar_sync(1, kEpiThreads);
-        rt_drain(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
+        rt_drain<kEpiThreads>(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
         named_bar_sync(1, kEpiThreads);
         if (valid) {
             // this thread's share of the row; the queue's corrections ride with the first half
@@ -459,13 +474,23 @@ int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_b
     float* dump = ctx->ransac_dump;
     const int dump_ld = ctx->ransac_dump_ld;
     cudaError_t e;
-    // 64-column tcgen05.ld: 650 vs 664 us per 100 000 x 16 345 registration; the sum is streamed only
-    // when the caller asked for cb_ransac's per-hypothesis `sums`
-    auto kern = dump ? ransac_tc_score_kernel<true, 32, true>
-                     : (want_sum ? ransac_tc_score_kernel<false, 64, true> : ransac_tc_score_kernel<false, 64, false>);
+    // the sum is streamed only when the caller asked for cb_ransac's per-hypothesis `sums`
+    static const int epi_warps = [] {
+        const char* e = getenv("CB_RT_EPI_WARPS");  // tuning knob: 8 or 16 epilogue warps
+        return e && atoi(e) == 8 ? 8 : kMaxEpiWarps;
+    }();
+    using kern_t = void (*)(const __nv_bfloat16*, const __nv_bfloat16*, const float*, const double*, const float4*,
+                            const float4*, int, int, int, int, int, double, const RansacState*, int32_t*, double*, float*, int);
+    kern_t kern;
+    if (epi_warps == 8)
+        kern = dump ? ransac_tc_score_kernel<true, 32, true, 8>
+                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, 8> : ransac_tc_score_kernel<false, 64, false, 8>);
+    else
+        kern = dump ? ransac_tc_score_kernel<true, 32, true, 16>
+                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, 16> : ransac_tc_score_kernel<false, 64, false, 16>);
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
     if (e == cudaSuccess)
-        kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), kThreads, kScoreSmem, st>>>(
+        kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), epi_warps * 32 + 64, kScoreSmem, st>>>(
             Apack, Bpack, band, Tw, src4, tgt4, m, cb_div_up(m, kRtTileN), tps, h0, w, thr2, state, pc, ps,
             dump ? dump + (size_t)h0 * dump_ld : nullptr, dump_ld);
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "ransac_tc_score_kernel: %s", cudaGetErrorString(e));

@@ -114,7 +114,11 @@ def eval_pose(T_est, T0, T1, axis_symmetry=1):
         trans = np.eye(4)
         trans[:3, :3] = _rot_y(i * (2 * np.pi / axis_symmetry))
         T_gt = np.matmul(T1, np.matmul(np.linalg.inv(trans), np.linalg.inv(T0))).astype(np.float32)
-        r_loss = np.arccos(np.clip((np.trace(T_est[:3, :3].t() @ T_gt[:3, :3]) - 1) / 2, -1, 1))
+        # float32 argument, arccos evaluated in float64: what the reference's pinned NumPy / torch did — the
+        # r_losses_* files it wrote (data/cache_ret) are float64 whose cosines are float32 values, the
+        # t_losses_* files float32 (tests/golden/cache_format.json).  Today's NumPy would return float32.
+        arg = np.float32(np.clip((np.trace(np.asarray(T_est[:3, :3].t() @ T_gt[:3, :3])) - 1) / 2, -1, 1))
+        r_loss = np.arccos(np.float64(arg))
         t_loss = np.linalg.norm(T_est[:3, 3] - T_gt[:3, 3])
         if r_loss_best > r_loss:
             r_loss_best = r_loss

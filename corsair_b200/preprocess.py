@@ -53,7 +53,7 @@ def chamfer_gpu(pc0, pc1):
     out = _chamfer(pc0, pc1, None, True)[0]
     if isinstance(pc0, torch.Tensor):
         return out.to(device=pc0.device, dtype=pc0.dtype)
-    return out.to(torch.float32)
+    return out.to(torch.float32).cpu()  # NumPy clouds: a host value (pc_dist.compute_dist stores it in a NumPy table)
 
 
 def chamfer_gpu_1direction(pc0, pc1):
@@ -72,21 +72,41 @@ def chamfer_kdtree_1direction(pc0, pc1):
 def quantize_pc(pc, voxel_size):
     """evaluation-shapenet.py:97-107 (and the library-side dedup of utils/Info/CADLib.py:106-121) on
     the device: one point per occupied voxel -> (pc [M,3] float32, pc_grid [M,3] int32) as tensors on
-    the input's device (CUDA for NumPy input).  Kept point = the first (lowest index) of its voxel,
-    output in ascending index order: ``np.unique(np.floor(pc / v), axis=0, return_index=True)`` with
-    the indices sorted.  MinkowskiEngine's own choice among duplicates cannot be checked here (not
-    installed): DESIGN.md lists this call as parity-unpinned."""
+    the input's device (CPU tensors for NumPy input, like the reference).  Kept point = the first
+    (lowest index) of its voxel, output in ascending index order.  That is MinkowskiEngine's rule:
+    sparse_quantize(return_index=True, return_maps_only=True) on the CPU goes through
+    CoordinateMapManagerCPU.insert_and_map (deps/MinkowskiEngine/src/coordinate_map_manager.cpp:56-69)
+    into CoordinateMapCPU::insert_and_map (src/coordinate_map_cpu.hpp:355-380), a sequential loop over
+    the rows that pushes a row index into the mapping only when its key is newly inserted.
+    The voxel keys ``floor(pc / voxel_size)`` are computed in the input's dtype like the reference
+    (float64 for the posed clouds of evaluation-shapenet.py:116-120)."""
     ctx = _capi.get_context()
-    p = ctx.dev(pc, torch.float32)
+    src = pc if isinstance(pc, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(pc))
+    on_cuda = src.is_cuda
+    if src.dtype == torch.float64:
+        # keys in float64 (a float32 division could put a point on the other side of a voxel face); the
+        # kernel then only has to floor exact integers
+        p64 = src.to(ctx.device)
+        if not on_cuda:
+            ctx.h2d_bytes += src.numel() * 8
+        keys = torch.floor(p64 / float(voxel_size)).to(torch.float32).contiguous()
+        p, vox = p64.to(torch.float32), 1.0
+    else:
+        p = ctx.dev(src, torch.float32)
+        keys, vox = p, float(voxel_size)
     n = p.shape[0]
     idx = ctx.empty((max(n, 1),), torch.int64)
     grid = ctx.empty((max(n, 1), 3), torch.int32)
     count = ctx.empty((1,), torch.int32)
-    ctx.call("cb_voxel_unique", ptr(p), n, float(voxel_size), ptr(idx), ptr(grid), ptr(count), ctx.stream)
+    ctx.call("cb_voxel_unique", ptr(keys), n, vox, ptr(idx), ptr(grid), ptr(count), ctx.stream)
     m = int(count.item())
     if m < 0:
         raise ValueError("quantize_pc: a coordinate is not finite or beyond 2^20 voxels")
-    return p[idx[:m]], grid[:m]
+    out_pc, out_grid = p[idx[:m]], grid[:m]
+    if not on_cuda:
+        ctx.d2h_bytes += out_pc.numel() * 4 + out_grid.numel() * 4
+        return out_pc.cpu(), out_grid.cpu()
+    return out_pc, out_grid
 
 
 def split_batch(C, F):

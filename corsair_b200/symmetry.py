@@ -146,7 +146,7 @@ def _pair_maps(K, second_sweep):
 
 
 def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *, n_hypotheses=100000,
-             adaptive=True, rng=None):
+             adaptive=True, rng=None, details=False):
     """utils/symmetry.py:262-358: pose with and without the symmetry-aided pairing search.
 
     ``rng``: where the segmentation's seed points come from instead of the global NumPy RNG the
@@ -158,7 +158,9 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     Everything after the seed-row draws — both segmentations, the vanilla registration and every
     pairing (kNN -> RANSAC -> Chamfer each) — is one cb_sym_pose call.
 
-    Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success)."""
+    Returns (T_est_best [4,4] f32 tensor, chamf_best float, T_est_ransac, chamf_ransac, success);
+    ``details=True`` appends a dict: ``best_index`` (0 = the vanilla registration, 1 + p = pairing p in the
+    order of :303-356), ``n_pairings`` evaluated and the call's ``status``."""
     ctx = _capi.get_context()
     baseF_d = ctx.dev(baseF, torch.float32)
     posF_d = ctx.dev(posF, torch.float32)
@@ -208,7 +210,10 @@ def sym_pose(baseF, xyz0, posF, xyz1, pos_sym, k_nn=5, max_corr=0.20, seed=0, *,
     if why is not None:
         tqdm.write(f"symmetry failed use ransac: {why}")
     T = torch.from_numpy(out[:34].astype(np.float32))
-    return T[:16].reshape(4, 4), float(out[16]), T[17:33].reshape(4, 4), float(out[33]), why is None
+    res = (T[:16].reshape(4, 4), float(out[16]), T[17:33].reshape(4, 4), float(out[33]), why is None)
+    if details:
+        res += (dict(best_index=int(out[35]), n_pairings=int(out[36]), status=status),)
+    return res
 
 
 # ---------------------------------------------------------------------------------------------

@@ -164,7 +164,11 @@ def eval_pose(T_est, T0, T1, axis_symmetry=1):
         trans = np.eye(4)
         trans[:3, :3] = rot_y_mat(i * (2 * np.pi / axis_symmetry))
         T_gt = (T1 @ (np.linalg.inv(trans) @ np.linalg.inv(T0))).astype(np.float32)
-        r = np.arccos(np.clip((np.trace(T_est[:3, :3].t() @ T_gt[:3, :3]) - 1) / 2, -1, 1))
+        # float32 argument, arccos in float64: the dtype / values of the r_losses_* caches the reference's own
+        # evaluation.py wrote (data/cache_ret: float64 whose cosines are float32 values); today's NumPy
+        # would keep float32 here
+        arg = np.float32(np.clip((np.trace(np.asarray(T_est[:3, :3].t() @ T_gt[:3, :3])) - 1) / 2, -1, 1))
+        r = np.arccos(np.float64(arg))
         t = np.linalg.norm(T_est[:3, 3] - T_gt[:3, 3])
         if r_best > r:
             r_best, t_best = r, t

@@ -124,3 +124,18 @@ def test_chamfer_table_half_and_ragged_sizes(ctx, rng, L, P):
     if L >= 4:
         assert np.array_equal(pc_dist.chamfer_rows_device(pts, 1, 3, half=True).cpu().numpy(), half[1:3])
         assert np.array_equal(pc_dist.chamfer_rows_device(pts, 1, 4).cpu().numpy(), full[1:4])
+
+
+@pytest.mark.parametrize("as_numpy", [True, False])
+def test_compute_dist_clouds_of_different_sizes(ctx, rng, as_numpy):
+    """utils/pc_dist.py:61-99 on a list of clouds that do NOT share a point count (the all-pairs kernel
+    needs equal sizes; the drop-in then runs one pair at a time): NumPy clouds and CPU tensors, against the
+    reference's loop restated on the KD-tree."""
+    from corsair_b200 import pc_dist
+    sizes = [300, 457, 300, 1200]
+    pcs = [cloud(rng, n) for n in sizes]
+    got = pc_dist.compute_dist(pcs if as_numpy else [torch.from_numpy(p) for p in pcs])
+    ref = port_retrieval.compute_dist([torch.from_numpy(p) for p in pcs])
+    assert isinstance(got, np.ndarray) and got.shape == (4, 4)
+    np.testing.assert_allclose(got, ref, rtol=1e-5)
+    assert np.array_equal(got, got.T) and np.all(np.diag(got) == 200)

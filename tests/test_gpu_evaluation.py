@@ -28,7 +28,9 @@ def _same(a, b):
             assert np.array_equal(np.asarray(x), np.asarray(y)), k
 
 
-def test_register_queries(ctx):
+def test_register_queries(ctx, tmp_path):
+    import json
+    import os
     from corsair_b200 import eval_pose, evaluation_registration as er, symmetry
     sc = _scene()
     bo, bx, bT, lo, lx, lT, sym, pos = sc
@@ -57,3 +59,11 @@ def test_register_queries(ctx):
         er.register_queries(*sc, workers=2)
     s, text = er.summarize(a)
     assert 0.0 <= s["rte_015_sym"] <= 1.0 and "rte 0.02" in text
+    # the files this sweep writes have the dtype / rank / trailing shape of the caches the reference's own
+    # evaluation.py wrote (data/cache_ret, recorded in tests/golden/cache_format.json)
+    fmt = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "cache_format.json")))["files"]
+    er.save_results(str(tmp_path), "chair", False, a)
+    for k in er.KEYS:
+        arr = np.load(tmp_path / f"{k}_chair_gt.npy")
+        dtype, ndim, trailing, _ = fmt[f"{k}_chair_gt.npy"]
+        assert (str(arr.dtype), arr.ndim, list(arr.shape[1:])) == (dtype, ndim, trailing), k

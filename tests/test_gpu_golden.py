@@ -101,3 +101,82 @@ def test_sym_pose_and_ransac_golden(ctx):
     np.testing.assert_allclose(got["T"].cpu().numpy(), r["T"], atol=1e-9)
     e = eval_pose.eval_pose(torch.from_numpy(g["T_est"]), g["T0"], g["T1"], 4)
     np.testing.assert_allclose(np.array(e), g["eval_pose_sym4"], rtol=1e-6)
+
+
+def test_find_corr_golden(ctx):
+    """utils/eval_pose.py:28-45 against the reference's own output: full clouds, and the seeded
+    global np.random.choice subsample (same draws, same order: base first, then pos)."""
+    from corsair_b200 import eval_pose
+    g = load("find_corr")
+    F0, F1 = torch.from_numpy(g["F0"]), torch.from_numpy(g["F1"])
+    a, b = eval_pose.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=250, subsample_size=-1)
+    assert np.array_equal(a, g["full_0"]) and np.array_equal(b, g["full_1"])
+    np.random.seed(5)
+    c, d = eval_pose.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=250, subsample_size=200)
+    assert np.array_equal(c, g["sub200_0"]) and np.array_equal(d, g["sub200_1"])
+    np.random.seed(6)
+    e, f = eval_pose.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=-1, subsample_size=700)
+    assert np.array_equal(e, g["sub700_0"]) and np.array_equal(f, g["sub700_1"])
+    # CUDA inputs (the reference runs it on device tensors): same rows
+    a2, b2 = eval_pose.find_corr(g["xyz0"], g["xyz1"], F0.cuda(), F1.cuda(), nn_max_n=250, subsample_size=-1)
+    assert np.array_equal(a2, g["full_0"]) and np.array_equal(b2, g["full_1"])
+
+
+@pytest.mark.parametrize("case", [0, 1, 2, 3, 4])
+def test_sym_pose_all_branches_golden(ctx, case):
+    """sym_pose against the reference's own run (tests/golden/make_round2_golden.py), UNCONDITIONALLY: three
+    tables with pos_sym >= 2 (K = 4: both sweeps of utils/symmetry.py:303-356, nine registrations, the mirrored
+    order [0,3,2,1]) and two chairs (K = 2).  The fixture's segmentation masks are asserted equal first, so the
+    pairing logic is pinned independently of k-means rounding ties; then the winning registration's index, both
+    poses and both Chamfer distances."""
+    from corsair_b200 import symmetry
+    g = load("sympose_k4")
+    pre = f"c{case}_"
+    pos_sym = int(g[pre + "pos_sym"])
+    K = 4 if pos_sym >= 2 else 2
+    np.random.seed(31)
+    bm = np.stack(symmetry.symmetric_cut4(g[pre + "baseF"], g[pre + "xyz0"], K))
+    pm = np.stack(symmetry.symmetric_cut4(g[pre + "posF"], g[pre + "xyz1"], K))
+    assert np.array_equal(bm, g[pre + "base_masks"]) and np.array_equal(pm, g[pre + "pos_masks"])
+    np.random.seed(31)
+    Tb, cb, Tr, cr, ok, det = symmetry.sym_pose(g[pre + "baseF"], g[pre + "xyz0"], g[pre + "posF"], g[pre + "xyz1"], pos_sym,
+                                                k_nn=5, max_corr=0.2, seed=31, details=True)
+    assert ok and det["status"] == 0 and det["n_pairings"] == len(g[pre + "T_all"]) - 1 == (2 * K if pos_sym >= 2 else K)
+    assert det["best_index"] == int(g[pre + "best_index"])
+    assert np.allclose(Tr.numpy(), g[pre + "T_ransac"], atol=1e-5) and abs(cr - float(g[pre + "ch_ransac"])) <= 1e-5 * cr
+    assert np.allclose(Tb.numpy(), g[pre + "T_best"], atol=1e-5) and abs(cb - float(g[pre + "ch_best"])) <= 1e-5 * cb
+    # the int-seed path (seed rows replayed in C, the path cb_sym_pose_many takes) gives the same answer
+    alt = symmetry.sym_pose(g[pre + "baseF"], g[pre + "xyz0"], g[pre + "posF"], g[pre + "xyz1"], pos_sym, k_nn=5, max_corr=0.2,
+                            seed=31, rng=31, details=True)
+    assert alt[5] == det and np.array_equal(alt[0].numpy(), Tb.numpy()) and alt[1] == cb
+
+
+@pytest.mark.parametrize("cat,K", [("chair", 2), ("table", 4)])
+def test_symmetric_cut4_ten_seeded_clouds(ctx, cat, K):
+    """symmetric_cut4 (utils/symmetry.py:182-259) on ten seeded clouds per category against the reference's own
+    masks: exact equality, no agreement rate.  For every cloud the test also lists which of the 100
+    neighbourhood k-means models differ from sklearn's (centres beyond 1e-6) and asserts that the ACCEPTED model
+    is the same one, so a residual difference could only come from models that lose the selection anyway."""
+    from corsair_b200 import symmetry
+    from oracle import port_symmetry
+    g = load("symcut")
+    report = []
+    for i in range(10):
+        F, xyz, ref = g[f"{cat}{i}_F"], g[f"{cat}{i}_xyz"], g[f"{cat}{i}_masks"]
+        np.random.seed(100 + i)
+        try:
+            got = np.stack(symmetry.symmetric_cut4(F, xyz, K))
+        except AttributeError:
+            got = np.zeros((0, len(xyz)), bool)
+        np.random.seed(100 + i)
+        cands, win = port_symmetry.cut_candidates(F, xyz, K)
+        picks = np.array([c["index"] for c in cands])
+        centers, stats, _ = symmetry.cut_model_device(ctx.dev(F, torch.float32), ctx.dev(xyz, torch.float32), K, picks, ctx)
+        centers = centers.cpu().numpy()
+        dwin = symmetry.select_cut(stats.cpu().numpy())
+        differ = [j for j, c in enumerate(cands) if np.abs(centers[j] - c["centers"]).max() > 1e-6]
+        report.append((i, win, dwin, differ))
+        assert dwin == win, f"{cat}{i}: accepted model {dwin} vs sklearn's {win}; differing models {differ}"
+        assert win not in differ, f"{cat}{i}: the accepted model's centres differ from sklearn's"
+        assert got.shape == ref.shape and np.array_equal(got, ref), f"{cat}{i}: masks differ (models differing: {differ})"
+    print(f"symmetric_cut4 {cat}: (cloud, sklearn winner, device winner, models whose centres differ) = {report}")

@@ -93,12 +93,35 @@ def test_quantize_pc_vs_oracle(ctx, rng, n, voxel):
         pc[-10:] = -np.abs(pc[-10:]) - 0.3         # negative voxels
     ref_pc, ref_grid, _ = ps.quantize_pc(pc, np.float32(voxel))
     got_pc, got_grid = preprocess.quantize_pc(pc, voxel)
-    assert got_pc.dtype == torch.float32 and got_grid.dtype == torch.int32 and got_pc.is_cuda
-    assert np.array_equal(got_pc.cpu().numpy(), ref_pc) and np.array_equal(got_grid.cpu().numpy(), ref_grid)
+    # NumPy in -> CPU tensors out, like the reference (torch.from_numpy(...).float() / .int())
+    assert got_pc.dtype == torch.float32 and got_grid.dtype == torch.int32 and not got_pc.is_cuda and not got_grid.is_cuda
+    assert np.array_equal(got_pc.numpy(), ref_pc) and np.array_equal(got_grid.numpy(), ref_grid)
     # CUDA input stays where it is; the synthetic generator's dedup is the same rule
-    again, _ = preprocess.quantize_pc(torch.from_numpy(pc).cuda(), voxel)
-    assert torch.equal(again, got_pc)
+    again, g2 = preprocess.quantize_pc(torch.from_numpy(pc).cuda(), voxel)
+    assert again.is_cuda and g2.is_cuda and torch.equal(again.cpu(), got_pc)
     assert np.array_equal(synth.voxel_dedup(pc, voxel), ref_pc)
+
+
+@pytest.mark.parametrize("n,voxel", [(257, 0.03), (20000, 0.03), (20000, 0.01)])
+def test_quantize_pc_float64_keys(ctx, rng, n, voxel):
+    """The reference floors pc / voxel_size in the INPUT dtype (evaluation-shapenet.py:97-99); its posed
+    clouds are float64 (:116-120).  A float32 division can put a point on the other side of a voxel face,
+    so float64 input must be keyed in float64: equal to np.unique(np.floor(pc / v)) of the float64 array,
+    including points planted a few float64 ulps either side of a face."""
+    from corsair_b200 import preprocess
+    pc = rng.standard_normal((n, 3)) * 0.4
+    faces = np.round(pc[:200] / voxel) * voxel
+    pc[:100] = np.nextafter(faces[:100], np.inf)       # just above a face
+    pc[100:200] = np.nextafter(faces[100:], -np.inf)    # just below
+    keys = np.floor(pc / voxel)
+    _, first = np.unique(keys, axis=0, return_index=True)
+    first = np.sort(first)
+    got_pc, got_grid = preprocess.quantize_pc(pc, voxel)
+    assert np.array_equal(got_grid.numpy(), keys[first].astype(np.int32))
+    assert np.array_equal(got_pc.numpy(), pc[first].astype(np.float32))
+    got32, _ = preprocess.quantize_pc(pc.astype(np.float32), voxel)   # float32 input: float32 keys, as NumPy would
+    k32 = np.floor(pc.astype(np.float32) / np.float32(voxel))
+    assert len(got32) == len(np.unique(k32, axis=0))
 
 
 def test_quantize_pc_edge_cases(ctx):

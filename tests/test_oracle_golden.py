@@ -191,3 +191,91 @@ def test_evaluation_cache_and_metric_tables(tmp_path):
     # hand-computed: thresholds are inclusive
     assert pe.compute_rte([0.02, 0.05, 0.2, 0.01]) == (0.5, 0.75, 0.75, 0.75)
     assert pe.compute_rre(np.deg2rad([4.0, 20.0, 50.0, 10.0])) == (0.25, 0.5, 0.75)
+
+
+def test_cache_files_match_the_reference_held_cache(tmp_path):
+    """the reference tree holds caches its own evaluation.py:420-441 wrote on the real
+    data (data/cache_ret).  tests/golden/cache_format.json records every file's dtype / rank / trailing shape
+    and tests/golden/cache_ret_head the first rows of the chair files (make_cache_format_golden.py): the
+    drop-in's loader must read them, and what it saves must have the same names, dtypes and shapes."""
+    import json
+    from corsair_b200 import evaluation_registration as er
+    here = os.path.join(os.path.dirname(__file__), "golden")
+    fmt = json.load(open(os.path.join(here, "cache_format.json")))
+    names = {f"{k}_{cat}{sfx}" for k in er.KEYS for cat in ("chair", "table") for sfx in ("_gt.npy", "_top1.npy")}
+    assert names == set(fmt["files"]), "the nine keys x category x suffix are exactly the reference's file names"
+    head = er.load_results(os.path.join(here, "cache_ret_head"), "chair", False)
+    assert head is not None and er.load_results(os.path.join(here, "cache_ret_head"), "chair", True) is None
+    assert len(head["Ts_est_best"]) == 12 and head["Ts_est_best"][0].shape == (4, 4)
+    for T in head["Ts_est_ransac"] + head["Ts_est_best"]:  # rigid poses: what eval_pose consumes
+        np.testing.assert_allclose(T[:3, :3] @ T[:3, :3].T, np.eye(3), atol=1e-5)
+        assert abs(np.linalg.det(T[:3, :3]) - 1) < 1e-5 and np.array_equal(T[3], [0, 0, 0, 1])
+    s, text = er.summarize(head)
+    assert 0 <= s["rre_005_sym"] <= 1 and "sym success rate" in text
+    # write them back through save_results: same names, dtypes, ranks and trailing shapes as the reference's files
+    er.save_results(str(tmp_path), "chair", False, head)
+    for k in er.KEYS:
+        name = f"{k}_chair_gt.npy"
+        a = np.load(tmp_path / name)
+        dtype, ndim, trailing, _ = fmt["files"][name]
+        assert (str(a.dtype), a.ndim, list(a.shape[1:])) == (dtype, ndim, trailing), name
+        assert np.array_equal(a, np.load(os.path.join(here, "cache_ret_head", name)))
+    # the means the reference prints for its chair cache (BASELINE.md section 2: 0.0613 / 0.0559, success 100 %)
+    m = fmt["chair_gt_means"]
+    assert abs(m["chamfer_dist_ransac"] - 0.0613) < 5e-4 and abs(m["chamfer_dist_sym"] - 0.0559) < 5e-4
+    assert m["sym_ransac_success"] == 1.0
+
+
+def test_find_corr_golden():
+    """utils/eval_pose.py:28-45: full clouds, and the seeded np.random.choice subsample."""
+    g = load("find_corr")
+    F0, F1 = torch.from_numpy(g["F0"]), torch.from_numpy(g["F1"])
+    a, b = port.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=250, subsample_size=-1)
+    assert np.array_equal(a, g["full_0"]) and np.array_equal(b, g["full_1"])
+    np.random.seed(5)
+    c, d = port.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=250, subsample_size=200)
+    assert np.array_equal(c, g["sub200_0"]) and np.array_equal(d, g["sub200_1"])
+    np.random.seed(6)
+    e, f = port.find_corr(g["xyz0"], g["xyz1"], F0, F1, nn_max_n=-1, subsample_size=700)
+    assert np.array_equal(e, g["sub700_0"]) and np.array_equal(f, g["sub700_1"])
+
+
+@pytest.mark.parametrize("case", [0, 3])
+def test_sym_pose_k4_golden(case):
+    """utils/symmetry.py:262-358 with both sweeps (case 0: table, pos_sym 4, nine registrations, the mirrored
+    order [0,3,2,1] of :326-356) and a chair (case 3): the oracle's restatement reproduces the reference's
+    masks, its winner and every registration's Chamfer distance."""
+    g = load("sympose_k4")
+    pre = f"c{case}_"
+    pos_sym = int(g[pre + "pos_sym"])
+    K = 4 if pos_sym >= 2 else 2
+    calls = []
+
+    def reg(src, tgt, max_corr, seed):
+        ms = ransac_np.draw_minimal_sets(len(src), 100000, 10, seed)
+        calls.append(ransac_c.ransac(src, tgt, max_corr, ms, adaptive=True)["T"])
+        return calls[-1]
+
+    np.random.seed(31)
+    bm = port_symmetry.symmetric_cut4(g[pre + "baseF"], g[pre + "xyz0"], K)
+    pm = port_symmetry.symmetric_cut4(g[pre + "posF"], g[pre + "xyz1"], K)
+    assert np.array_equal(np.stack(bm), g[pre + "base_masks"]) and np.array_equal(np.stack(pm), g[pre + "pos_masks"])
+    np.random.seed(31)
+    Tb, cb, Tr, cr, ok = port_symmetry.sym_pose(g[pre + "baseF"], g[pre + "xyz0"], g[pre + "posF"], g[pre + "xyz1"], pos_sym,
+                                                k_nn=5, max_corr=0.2, seed=31, registration=reg)
+    assert ok and len(calls) == len(g[pre + "T_all"]) == (1 + 2 * K if pos_sym >= 2 else 1 + K)
+    np.testing.assert_allclose(np.stack(calls), g[pre + "T_all"], atol=1e-12)
+    assert np.allclose(Tb.numpy(), g[pre + "T_best"], atol=1e-6) and cb == pytest.approx(float(g[pre + "ch_best"]), rel=1e-9)
+    assert np.allclose(Tr.numpy(), g[pre + "T_ransac"], atol=1e-6) and cr == pytest.approx(float(g[pre + "ch_ransac"]), rel=1e-9)
+    assert np.allclose(Tb.numpy(), g[pre + "T_all"][int(g[pre + "best_index"])].astype(np.float32), atol=1e-6)
+
+
+@pytest.mark.parametrize("name,K", [("chair0", 2), ("chair3", 2), ("table1", 4), ("table6", 4)])
+def test_symmetric_cut4_seeded_clouds(name, K):
+    g = load("symcut")
+    np.random.seed(100 + int(name[-1]))
+    try:
+        masks = np.stack(port_symmetry.symmetric_cut4(g[name + "_F"], g[name + "_xyz"], K))
+    except AttributeError:
+        masks = np.zeros((0, len(g[name + "_xyz"])), bool)
+    assert np.array_equal(masks, g[name + "_masks"])
