@@ -89,7 +89,10 @@ def quantize_pc(pc, voxel_size):
         p64 = src.to(ctx.device)
         if not on_cuda:
             ctx.h2d_bytes += src.numel() * 8
-        keys = torch.floor(p64 / float(voxel_size)).to(torch.float32).contiguous()
+        # a DEVICE tensor as divisor: torch turns division by a host scalar into multiplication by its
+        # reciprocal, which is not the correctly rounded quotient NumPy computes
+        vox64 = torch.full((1,), float(voxel_size), dtype=torch.float64, device=ctx.device)
+        keys = torch.floor(p64 / vox64).to(torch.float32).contiguous()
         p, vox = p64.to(torch.float32), 1.0
     else:
         p = ctx.dev(src, torch.float32)

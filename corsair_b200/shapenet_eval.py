@@ -18,7 +18,9 @@ import torch
 from . import _capi
 from ._capi import ptr
 from .eval_pose import eval_pose
-from .symmetry import _worker_tls, sym_pose
+from .symmetry import sym_pose
+
+_worker_tls = __import__("threading").local()  # per-thread CUDA stream of register_many's workers
 
 SYM_ORDERS = (12, 8, 6, 4, 3, 2, 1)  # evaluation-shapenet.py:151 (1 = no symmetry)
 
