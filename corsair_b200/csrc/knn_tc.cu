@@ -185,7 +185,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + A_BYTES + NB * B_BYTES);
     float* s_top = reinterpret_cast<float*>(smem + A_BYTES + NB * B_BYTES + 128);  // [kColParts][kTileM][KC]
     int* s_cnt = reinterpret_cast<int*>(s_top + kColParts * kTileM * KC);        // [kTileM]
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = tc::uniform_warp_idx(), lane = threadIdx.x & 31;
     const int c = blockIdx.y;
     const int t0 = (c * chunk) / kTileN;
     const int t1 = min((nr + kTileN - 1) / kTileN, ((c + 1) * chunk) / kTileN);
@@ -227,17 +227,18 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
             }
         }
     } else if (warp == kEpiWarps + 1) {
-        // ===== MMA issuer: one thread =====
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::idesc_bf16(kTileM, kTileN);
-            const uint32_t a_addr = tc::smem_u32(sA);
-            tc::mbar_wait(&ctl->a_full, 0);
-            for (int it = 0; it < nsteps; ++it) {
-                const int st = it % NB, use = it / NB;   // shared-memory stage
-                const int ts = it & 1, tuse = it >> 1;   // tensor-memory stage
-                tc::mbar_wait(&ctl->full[st], use & 1);
-                tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
-                tc::fence_after_sync();
+        // ===== MMA issuer: the whole warp walks the loop (uniform control flow), one elected lane issues =====
+        constexpr uint32_t idesc = tc::idesc_bf16(kTileM, kTileN);
+        const uint32_t a_addr = tc::smem_u32(sA);
+        const bool leader = tc::elect_one();
+        tc::mbar_wait(&ctl->a_full, 0);
+        for (int it = 0; it < nsteps; ++it) {
+            const int st = it % NB, use = it / NB;   // shared-memory stage
+            const int ts = it & 1, tuse = it >> 1;   // tensor-memory stage
+            tc::mbar_wait(&ctl->full[st], use & 1);
+            tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
+            tc::fence_after_sync();
+            if (leader) {
                 const uint32_t b_addr = tc::smem_u32(sB + st * B_BYTES);
 #pragma unroll
                 for (int ks = 0; ks < KP / 16; ++ks) {
@@ -248,6 +249,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                 tc::mma_commit(&ctl->empty[st]);      // smem stage reusable once these MMAs finish
                 tc::mma_commit(&ctl->tmem_full[ts]);  // accumulator ready for the epilogue
             }
+            __syncwarp();
         }
     } else {
         // ===== epilogue: 512 threads = 128 query rows (TMEM lanes) x 4 column quarters =====

@@ -207,7 +207,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
     double* s_dsum = reinterpret_cast<double*>(list + kListCap);
     double* s_dcnt = s_dsum + kHT * kRtTileM;
     RtCtl* ctl = reinterpret_cast<RtCtl*>(s_dcnt + kHT * kRtTileM);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = tc::uniform_warp_idx(), lane = threadIdx.x & 31;
     const int t0 = blockIdx.y * tiles_per_split;
     const int t1 = min(ntiles_total, t0 + tiles_per_split);
     const int ntiles = t1 - t0;
@@ -248,18 +248,19 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             }
         }
     } else if (warp == kEpiWarps + 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::idesc_bf16(kRtTileM, kRtTileN);
-            constexpr uint32_t LBO = (kRtTileM / 8) * 128;  // both operands: 128-row tiles
-            const uint32_t a_addr = tc::smem_u32(sA);
-            tc::mbar_wait(&ctl->a_full, 0);
-            for (int it = 0; it < ntiles; ++it) {
-                const int st = it % kStages, use = it / kStages;
-                const int ts = it & 1, tuse = it >> 1;
-                tc::mbar_wait(&ctl->full[st], use & 1);
-                tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
-                tc::fence_after_sync();
+        // ===== MMA issuer: the whole warp walks the loop (uniform control flow), one elected lane issues =====
+        constexpr uint32_t idesc = tc::idesc_bf16(kRtTileM, kRtTileN);
+        constexpr uint32_t LBO = (kRtTileM / 8) * 128;  // both operands: 128-row tiles
+        const uint32_t a_addr = tc::smem_u32(sA);
+        const bool leader = tc::elect_one();
+        tc::mbar_wait(&ctl->a_full, 0);
+        for (int it = 0; it < ntiles; ++it) {
+            const int st = it % kStages, use = it / kStages;
+            const int ts = it & 1, tuse = it >> 1;
+            tc::mbar_wait(&ctl->full[st], use & 1);
+            tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
+            tc::fence_after_sync();
+            if (leader) {
                 const uint32_t b_addr = tc::smem_u32(sB + st * kBTileBytes);
 #pragma unroll
                 for (int a = 0; a < kHT; ++a) {
@@ -273,6 +274,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                 tc::mma_commit(&ctl->empty[st]);
                 tc::mma_commit(&ctl->tmem_full[ts]);
             }
+            __syncwarp();
         }
     } else {
         // ===== epilogue: one thread per hypothesis row and column part =====

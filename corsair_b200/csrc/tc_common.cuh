@@ -11,6 +11,26 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// ---- warp-uniform role dispatch ----------------------------------------------------------------
+// The warp index as a value the compiler can prove uniform (shuffle from lane 0): branches on it are
+// uniform branches, so a role's loop counters, descriptors and barrier addresses live in uniform
+// registers.  With `threadIdx.x >> 5` and an `if (lane == 0)` around a whole role, every tcgen05.mma was
+// wrapped in an R2UR + ELECT + BRA.U.ANY waterfall: 169 instructions per 12 MMAs, issued by one warp that
+// competes with the epilogue warps of its scheduler (SASS / ncu, round 2).
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+// true in exactly one (the same, as long as all 32 lanes stay active) lane of a converged warp
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- mbarrier ---------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
