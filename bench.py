@@ -478,7 +478,8 @@ def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, m
                              "drawn from the real label histogram (K = 4 and nine registrations when >= 2), device-resident"}
 
     # ---- e3: one C5-sized RANSAC (M = 250 000, H = 4096) with the hypothesis range split over the ranks
-    a = c5[0][0]
+    p3 = synth.make_pair(500, args.feature_dim, "table", n_raw=50000, n_cad=10000)  # the SAME pair on every rank
+    a = [torch.from_numpy(p3[k]).to(dev) for k in ("baseF", "xyz0", "posF", "xyz1")]
     idx = find_nn.knn_device(a[0], a[2], K_NN)
     si = torch.repeat_interleave(torch.arange(a[0].shape[0], device=dev), K_NN)
     ti = idx.reshape(-1)

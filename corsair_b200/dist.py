@@ -68,25 +68,28 @@ def merge_topk(idx_local, dist_local, shard_lo, k):
 def merge_best_hypothesis(T, stats, h_lo):
     """Merge per-shard RANSAC results.  T [4,4] f64, stats [4] f64 = (best_h local to the shard,
     inliers, sum_d2, n_evaluated); h_lo = first hypothesis of this rank's range.  Returns the
-    winning (T, stats with the GLOBAL hypothesis index and the summed n_evaluated)."""
+    winning (T, stats with the GLOBAL hypothesis index and the summed n_evaluated).  The records stay
+    on the tensors' device: one all-gather of 21 doubles per rank, then Open3D's order (count desc,
+    rmse asc) with the lowest global hypothesis index on exact ties as three masked reductions."""
     rec = torch.cat([T.reshape(-1).to(torch.float64), stats.to(torch.float64),
                      torch.tensor([float(h_lo)], dtype=torch.float64, device=T.device)])
-    recs = torch.stack(_all_gather(rec)).cpu().numpy()
-    best, key = None, None
-    total_eval = 0.0
-    for r in recs:
-        h, cnt, s2, nev, lo = r[16], r[17], r[18], r[19], r[20]
-        total_eval += nev
-        if h < 0:
-            continue
-        rmse = np.sqrt(s2 / cnt) if cnt > 0 else 0.0
-        cand = (-cnt, rmse, h + lo)
-        if key is None or cand < key:
-            key, best = cand, r
-    if best is None:
-        return torch.eye(4, dtype=torch.float64, device=T.device), torch.tensor([-1.0, 0.0, 0.0, total_eval], dtype=torch.float64, device=T.device)
-    Tm = torch.tensor(best[:16].reshape(4, 4), dtype=torch.float64, device=T.device)
-    st = torch.tensor([best[16] + best[20], best[17], best[18], total_eval], dtype=torch.float64, device=T.device)
+    recs = torch.stack(_all_gather(rec))                       # [world, 21]
+    h, cnt, s2, nev, lo = recs[:, 16], recs[:, 17], recs[:, 18], recs[:, 19], recs[:, 20]
+    total_eval = nev.sum()
+    valid = h >= 0
+    inf = torch.full_like(cnt, float("inf"))
+    cnt_v = torch.where(valid, cnt, -inf)
+    rmse = torch.where(cnt > 0, torch.sqrt(s2 / cnt.clamp(min=1.0)), torch.zeros_like(cnt))
+    top = valid & (cnt_v == cnt_v.max())
+    top = top & (rmse == torch.where(top, rmse, inf).min())
+    gh = h + lo
+    win = torch.argmin(torch.where(top, gh, inf))
+    none = ~valid.any()
+    best = recs[win]
+    Tm = torch.where(none, torch.eye(4, dtype=torch.float64, device=T.device), best[:16].reshape(4, 4))
+    st = torch.stack([torch.where(none, torch.full_like(total_eval, -1.0), best[16] + best[20]),
+                      torch.where(none, torch.zeros_like(total_eval), best[17]),
+                      torch.where(none, torch.zeros_like(total_eval), best[18]), total_eval])
     return Tm, st
 
 
