@@ -12,7 +12,7 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libcorsair_b200.so")
+LIB_PATH = os.environ.get("CORSAIR_B200_LIB") or os.path.join(_HERE, "lib", "libcorsair_b200.so")  # env: tuning builds
 
 _lib = None
 _lib_lock = threading.Lock()

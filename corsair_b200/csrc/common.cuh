@@ -97,6 +97,21 @@ static inline T* cb_alloc_t(cb_ctx* ctx, size_t n) {
 
 static inline int cb_div_up(int a, int b) { return (a + b - 1) / b; }
 
+// ---- debug build (make debug -> lib/libcorsair_b200_dbg.so): device-side range checks -----------
+// compute-sanitizer is closed on the GPU pool this was developed on; the debug library traps (the
+// launch then fails loudly) when an index the multi-role kernels compute leaves its range.
+#ifdef CB_DEBUG_CHECKS
+#define CB_DEV_CHECK(cond)                                                        \
+    do {                                                                          \
+        if (!(cond)) {                                                            \
+            printf("corsair_b200 device check failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__); \
+            __trap();                                                             \
+        }                                                                         \
+    } while (0)
+#else
+#define CB_DEV_CHECK(cond) ((void)0)
+#endif
+
 // ---- device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ uint64_t cb_splitmix64(uint64_t x) {
     x += 0x9E3779B97F4A7C15ull;

@@ -192,10 +192,10 @@ __device__ __forceinline__ void knn_cp_async_wait() {
 // high word of the key, low word among the lanes that match, index among those that still match.
 template <int SL>
 __global__ void __launch_bounds__(256)
-knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int d, int dq_stride,
+knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__ r, int nr_total, int d, int dq_stride,
                   int k, int metric, const int32_t* __restrict__ cand_idx, const float* __restrict__ cand_s,
                   int S, int KC, const float* __restrict__ bound, const unsigned int* __restrict__ rmax_bits,
-                  double gamma, const int32_t* __restrict__ unscramble,
+                  double gamma, const int32_t* __restrict__ unscramble, int unscramble_n,
                   int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist,
                   int32_t* __restrict__ fb_list, int* __restrict__ fb_count) {
     __shared__ float s_rows[8][32][kRowPad];
@@ -214,7 +214,10 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
     for (int t = 0; t < SL; ++t) {
         const int ci = lane + 32 * t;
         int j = ci < ncand ? cand_idx[(size_t)qi * ncand + ci] : -1;
-        if (unscramble && j >= 0) j = unscramble[j];
+        if (unscramble && j >= 0) {
+            CB_DEV_CHECK(j < unscramble_n);
+            j = unscramble[j];
+        }
         id[t] = 0x7fffffff;
         key[t] = ~0ull;
         if (!__ballot_sync(0xffffffffu, j >= 0)) continue;
@@ -222,6 +225,7 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
 #pragma unroll 8
         for (int rr = 0; rr < 32; ++rr) {
             const int jj = __shfl_sync(0xffffffffu, j, rr);
+            CB_DEV_CHECK(jj < nr_total);
             if (jj >= 0 && lane < d) knn_cp_async4(&rows[rr][lane], r + (size_t)jj * dq_stride + lane);
         }
         knn_cp_async_wait();
@@ -484,8 +488,8 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
         const int SL = cb_div_up(S * LC, 32);
         auto kern = SL <= 1 ? knn_rerank_kernel<1> : SL <= 2 ? knn_rerank_kernel<2> : SL <= 4 ? knn_rerank_kernel<4>
                                                                                                : knn_rerank_kernel<8>;
-        kern<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, d, stride, k, metric, ci, cs, S, LC, use_tc ? bound : nullptr,
-                                               scal, gamma, unscramble, idx, idx32, dist, fb, (int*)(scal + 1));
+        kern<<<cb_div_up(nq, 8), 256, 0, st>>>(qd, nq, rd, nr, d, stride, k, metric, ci, cs, S, LC, use_tc ? bound : nullptr,
+                                               scal, gamma, unscramble, cb_div_up(nr, 256) * 256, idx, idx32, dist, fb, (int*)(scal + 1));
         CB_LAUNCH_CHECK(ctx);
     }
     knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, stride, k, metric, fb,

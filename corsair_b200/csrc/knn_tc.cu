@@ -172,7 +172,7 @@ struct TcSmemCtl {
 template <int D, int KC, int NB>
 __global__ void __launch_bounds__(kThreads, 1)
 knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack, int nq, int nr,
-              int chunk, int S, int maxdot, int32_t* __restrict__ cand_idx, float* __restrict__ bound) {
+              int chunk, int S, int maxdot, int nr_pad, int32_t* __restrict__ cand_idx, float* __restrict__ bound) {
     constexpr int KP = kprime(D);
     constexpr int LC = 6 * KC;            // list slots per (query, chunk): P(overflow) ~ 3e-7
     constexpr int GROUP = 8;              // columns per group maximum (16 let 4 % of the rows of clustered
@@ -205,6 +205,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
         }
         tc::fence_barrier_init();
     }
+    CB_DEV_CHECK(ntiles >= 1 && t1 * kTileN <= nr_pad);
     if (threadIdx.x < kTileM) s_cnt[threadIdx.x] = 0;
     if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 512);
     tc::fence_before_sync();
@@ -349,6 +350,7 @@ knn_tc_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __re
                         const int e = __ffs(mask) - 1;
                         mask &= mask - 1;
                         const int pos = atomicAdd(&s_cnt[row], 1);
+                        CB_DEV_CHECK(pos >= 0 && col0 + h * 32 + e < nr_pad && e >= 0 && e < 32);
                         if (pos < LC) cand_idx[o + pos] = col0 + h * 32 + e;  // scrambled column: the re-rank maps it back
                     }
                 }
@@ -377,7 +379,7 @@ constexpr int b_stages() {
 
 template <int D, int KC>
 cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, int nr, int chunk, int S, int maxdot,
-                      int32_t* ci, float* bound, cudaStream_t st) {
+                      int nr_pad, int32_t* ci, float* bound, cudaStream_t st) {
     constexpr int KP = kprime(D);
     constexpr int NB = b_stages<D, KC>();
     static_assert(NB >= 2, "at least two B stages");
@@ -385,7 +387,7 @@ cudaError_t launch_tc(const __nv_bfloat16* A, const __nv_bfloat16* B, int nq, in
     cudaError_t e = cudaFuncSetAttribute(knn_tc_kernel<D, KC, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((nq + kTileM - 1) / kTileM, S);
-    knn_tc_kernel<D, KC, NB><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, ci, bound);
+    knn_tc_kernel<D, KC, NB><<<grid, kThreads, smem, st>>>(A, B, nq, nr, chunk, S, maxdot, nr_pad, ci, bound);
     return cudaGetLastError();
 }
 
@@ -431,10 +433,10 @@ int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int 
         knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, unscramble, rmax_bits);
     CB_LAUNCH_CHECK(ctx);
     cudaError_t e;
-    if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
-    else if (dp == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
-    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
-    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, cand_idx, bound, st);
+    if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, nr_pad, cand_idx, bound, st);
+    else if (dp == 16) e = launch_tc<16, 16>(A, B, nq, nr, chunk, S, maxdot, nr_pad, cand_idx, bound, st);
+    else if (KC == 8) e = launch_tc<32, 8>(A, B, nq, nr, chunk, S, maxdot, nr_pad, cand_idx, bound, st);
+    else e = launch_tc<32, 16>(A, B, nq, nr, chunk, S, maxdot, nr_pad, cand_idx, bound, st);
     ctx->launches++;
     if (e != cudaSuccess) CB_FAIL(ctx, CB_ECUDA, "knn_tc_kernel launch failed: %s", cudaGetErrorString(e));
     return CB_OK;

@@ -147,7 +147,10 @@ __device__ __forceinline__ unsigned rt_sign(float u) { return __float_as_uint(u)
 // so that both pipes share the epilogue: column c takes the float path when bit 1 of c is clear
 constexpr float kNegBig = -1.2676506e30f;  // -2^100: fma.sat(u, kNegBig, 0) = 1 for u < 0, else 0
 __device__ __forceinline__ float rt_gate(float u) { return fma_sat(u, kNegBig, 0.f); }
-__device__ __forceinline__ bool rt_float_path(int col) { return (col & 2) == 0; }
+#ifndef CB_RT_FLOAT_SHARE
+#define CB_RT_FLOAT_SHARE 2  // quarters of the columns counted on the FMA pipe (0..4)
+#endif
+__device__ __forceinline__ bool rt_float_path(int col) { return ((col >> 1) & 3) < CB_RT_FLOAT_SHARE; }
 __device__ __forceinline__ double rt_streamed_count(int col, float u) {
     return rt_float_path(col) ? (double)rt_gate(u) : (double)rt_sign(u);
 }
@@ -180,6 +183,7 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
     for (int i = threadIdx.x; i < nlist; i += kEpiThreads) {
         const int2 en = list[i];
         const int row = (en.x >> 24) & 0xff, col = en.x & 0xffffff;
+        CB_DEV_CHECK(col < (1 << 24) && row < kHT * kRtTileM);
         double dc, ds;
         rt_exact_delta(Tw + (size_t)min(jcta + row, w - 1) * 12, src4, tgt4, col, __int_as_float(en.y), thr2d, dc, ds);
         atomicAdd(&s_dcnt[row], dc);
@@ -294,7 +298,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             float bm0 = INFINITY, bm1 = INFINITY;
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
-                if (e & 2) cnt_i += rt_sign(v[e]) + rt_sign(v[e + 1]);
+                if (!rt_float_path(e)) cnt_i += rt_sign(v[e]) + rt_sign(v[e + 1]);
                 else c2 = add2(c2, pk2(rt_gate(v[e]), rt_gate(v[e + 1])));
                 // the streamed sum only feeds cb_ransac's optional `sums` output: the fold recomputes the
                 // sum of every hypothesis tied at the top count exactly
@@ -325,6 +329,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
                     float u = 0.f;  // v[e] by static selects: a runtime index would put v in local memory
 #pragma unroll
                     for (int t = 0; t < 32; ++t) u = t == e ? v[t] : u;
+                    CB_DEV_CHECK(pos >= 0 && rloc >= 0 && rloc < kHT * kRtTileM && colc + e < m && colc + e < (1 << 24));
                     if (pos < kListCap) list[pos] = make_int2((rloc << 24) | (colc + e), __float_as_int(u));
                     else rt_overflow(colc + e, u, Tj, src4, tgt4, thr2d, dcnt, dsum);
                     ++pos;
