@@ -30,10 +30,11 @@ def test_feature_rows_top50(ctx, rng, d):
 @pytest.mark.parametrize("category,K", [("chair", 2), ("table", 4)])
 def test_symmetric_cut4_masks(ctx, category, K):
     """Masks of the device segmentation vs the reference algorithm (sklearn KMeans) under the same
-    global NumPy seed.  BLAS summation order inside sklearn is not reproducible, so the bar is
-    the mask-equality rate over the cloud, which must be ~1."""
+    global NumPy seed on three full-size clouds: EQUAL masks (round 1 asserted an agreement rate; the
+    device k-means replays sklearn's float32 operations step by step and no cloud tried since has
+    differed — tests/test_gpu_golden.py::test_symmetric_cut4_ten_seeded_clouds lists per-model
+    differences if one ever does)."""
     from corsair_b200 import symmetry
-    agree, total, same_winner = 0, 0, 0
     for seed in range(3):
         p = synth.make_pair(seed, 32, category)
         np.random.seed(31)
@@ -43,12 +44,7 @@ def test_symmetric_cut4_masks(ctx, category, K):
         got = symmetry.symmetric_cut4(p["posF"], p["xyz1"], K)
         assert len(got) == K and all(m.dtype == bool and m.shape == (len(p["xyz1"]),) for m in got)
         assert np.stack(got).sum(0).min() == 1 and np.stack(got).sum(0).max() == 1  # a partition
-        # k-means labels are a permutation class: compare partitions, and for K=4 the cyclic order
-        eq = np.mean([np.array_equal(a, b) for a, b in zip(np.stack(got).T, np.stack(ref).T)])
-        agree += eq
-        total += 1
-        same_winner += int(eq > 0.99)
-    assert same_winner >= 2, f"device segmentation agrees with the reference on {same_winner}/3 clouds"
+        assert np.array_equal(np.stack(got), np.stack(ref)), f"seed {seed}: masks differ from sklearn's"
 
 
 @pytest.mark.parametrize("category,K", [("chair", 2), ("table", 4), ("chair", 4), ("table", 2)])
@@ -126,28 +122,44 @@ def test_kmeans_batch_stats_vs_sklearn(ctx):
 
 @pytest.mark.parametrize("category", ["chair", "table"])
 def test_sym_pose_matches_oracle(ctx, category):
+    """sym_pose against the oracle's restatement on a full-size pair (chair: K = 2, three registrations;
+    table: pos_sym = 4, K = 4, nine).  The oracle is handed the DEVICE segmentation (masks of
+    symmetry.symmetric_cut4 under the same NumPy seed), so the pairing logic — both sweeps, the mirrored
+    order, the strictly-lower-Chamfer selection — is compared unconditionally and independently of k-means
+    rounding ties; the masks themselves are pinned against the reference in test_gpu_golden.py."""
     from corsair_b200 import symmetry
     p = synth.make_pair(11, 32, category)
+    K = 4 if p["pos_sym"] >= 2 else 2
+    calls = []
 
     def reg(src, tgt, max_corr, seed):
         ms = ransac_np.draw_minimal_sets(len(src), 100000, 10, seed)
-        return ransac_c.ransac(src, tgt, max_corr, ms, adaptive=True)["T"]
+        calls.append(ransac_c.ransac(src, tgt, max_corr, ms, adaptive=True)["T"])
+        return calls[-1]
 
     np.random.seed(31)
+    dev_masks = [symmetry.symmetric_cut4(p["baseF"], p["xyz0"], K), symmetry.symmetric_cut4(p["posF"], p["xyz1"], K)]
+    it = iter(dev_masks)
     ref = port_symmetry.sym_pose(p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"], k_nn=5,
-                                 max_corr=0.2, seed=31, registration=reg,
+                                 max_corr=0.2, seed=31, registration=reg, cut=lambda f, x, k, max_sample=100: next(it),
                                  find_kcorr=lambda a, b, k, subsample_size: (np.repeat(np.arange(len(a)), k), port.find_knn_exact(a, b, k)[0].reshape(-1)))
+    chs = [port.chamfer_kdtree_1direction(port.apply_transform(p["xyz0"], torch.from_numpy(T.astype(np.float32))), p["xyz1"]) for T in calls]
+    best = 0
+    for i in range(1, len(chs)):
+        if chs[best] > chs[i]:
+            best = i
     np.random.seed(31)
-    got = symmetry.sym_pose(p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"], k_nn=5, max_corr=0.2, seed=31)
+    got = symmetry.sym_pose(p["baseF"], p["xyz0"], p["posF"], p["xyz1"], p["pos_sym"], k_nn=5, max_corr=0.2, seed=31, details=True)
     assert isinstance(got[0], torch.Tensor) and got[0].dtype == torch.float32 and got[0].shape == (4, 4)
     assert isinstance(got[1], float) and isinstance(got[3], float) and got[4] is True and ref[4] is True
+    assert len(calls) == (1 + 2 * K if p["pos_sym"] >= 2 else 1 + K) == got[5]["n_pairings"] + 1
     # vanilla branch: same correspondences and minimal sets -> same pose, same Chamfer
     assert torch.allclose(got[2], ref[2], atol=1e-5)
     assert abs(got[3] - ref[3]) <= 1e-5 * ref[3]
-    # symmetry-aided branch: equal when the segmentation agrees (see test_symmetric_cut4_masks)
-    assert got[1] <= got[3] + 1e-12
-    if abs(got[1] - ref[1]) <= 1e-5 * ref[1]:
-        assert torch.allclose(got[0], ref[0], atol=1e-5)
+    # symmetry-aided branch, unconditionally: the same winner, its pose, its Chamfer distance
+    assert got[5]["best_index"] == best
+    assert abs(got[1] - ref[1]) <= 1e-5 * ref[1]
+    assert torch.allclose(got[0], ref[0], atol=1e-5)
 
 
 def test_sym_pose_fallback_when_segmentation_fails(ctx, rng):
