@@ -433,9 +433,9 @@ ransac_fold_kernel(int32_t* __restrict__ pc, double* __restrict__ ps, int P, con
     const int prev_count = state->best_count;
     if (tid == 0) {
         // evaluations (hypothesis x correspondence) the scoring launch of this wave performed: its CTAs
-        // of 256 hypotheses whose first hypothesis lay below the budget it saw (= budget_in: the previous
+        // of kRtCtaHyps hypotheses whose first hypothesis lay below the budget it saw (= budget_in: the previous
         // fold finished before that launch started)
-        const int scored = min(w, ((min(budget_in, h0 + w) - h0 + 255) / 256) * 256);
+        const int scored = min(w, ((min(budget_in, h0 + w) - h0 + kRtCtaHyps - 1) / kRtCtaHyps) * kRtCtaHyps);
         dev_work[CB_T_RANSAC_SCORE] += (double)scored * (double)m;
         dev_work[CB_T_RANSAC_WAVES] += 1.0;
         s_stop = h0 + w;

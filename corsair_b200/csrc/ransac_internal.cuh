@@ -46,6 +46,13 @@ constexpr int kRtKP = 96;        // widened K axis (6 MMAs of K = 16)
 constexpr int kRtTileM = 128;    // hypotheses per MMA (TMEM lanes)
 constexpr int kRtTileN = 128;    // correspondences per MMA / B tile
 constexpr int kRtTerms = 15;
+// A tiles (of 128 hypotheses) per scoring CTA.  2: one CTA per SM (512 TMEM columns, 221 KB of shared
+// memory); 1: two CTAs per SM (256 columns, 106 KB each) whose pipelines interleave.
+#ifndef CB_RT_HT
+#define CB_RT_HT 2
+#endif
+constexpr int kRtHT = CB_RT_HT;
+constexpr int kRtCtaHyps = kRtHT * kRtTileM;  // hypotheses per scoring CTA
 
 __device__ __forceinline__ __nv_bfloat16 rt_bf16(double x) { return __float2bfloat16_rn((float)x); }
 __device__ __forceinline__ void rt_split2(double x, __nv_bfloat16& hi, __nv_bfloat16& lo) {

@@ -28,14 +28,14 @@
 
 namespace {
 
-constexpr int kHT = 2;            // A tiles (of 128 hypotheses) per CTA
-constexpr int kStages = 6;        // shared-memory ring of 24 KB B tiles: the copies of five tiles in flight cover the L2 latency
-// epilogue warps: 4 lane quadrants x 2 A tiles x (EW / 8) column parts.  16 (four per SM sub-partition)
+constexpr int kHT = kRtHT;        // A tiles (of 128 hypotheses) per CTA
+constexpr int kStages = kHT == 2 ? 6 : 3;  // shared-memory ring of 24 KB B tiles
+// epilogue warps: 4 lane quadrants x kHT A tiles x (EW / (4 kHT)) column parts.  16 (four per SM sub-partition)
 // is the default: with 8 the kernel was bound by the epilogue's dependent-issue latency (ncu, round 2:
 // issue active 48 %, tensor pipe 49 %, warps active 15.6 %, stall `wait` 1.0 per issue)
-constexpr int kMaxEpiWarps = 16;
-constexpr int kListCap = 2048;    // queued in-band evaluations per CTA (overflow is settled inline)
-constexpr int kListDrain = 1024;  // drain the queue at the next tile boundary once it holds this many
+constexpr int kMaxEpiWarps = 8 * kHT;
+constexpr int kListCap = kHT == 2 ? 2048 : 1024;  // queued in-band evaluations per CTA (overflow is settled inline)
+constexpr int kListDrain = kListCap / 2;          // drain the queue at the next tile boundary once it holds this many
 constexpr uint32_t kATileBytes = kRtTileM * kRtKP * 2;  // 24 KB
 constexpr uint32_t kBTileBytes = kRtTileN * kRtKP * 2;  // 24 KB
 
@@ -192,13 +192,13 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
 }
 
 template <bool DUMP, int LDW, bool WSUM, int kEpiWarps>
-__global__ void __launch_bounds__(kEpiWarps * 32 + 64, 1)
+__global__ void __launch_bounds__(kEpiWarps * 32 + 64, kHT == 2 ? 1 : 2)
 ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
                        const float* __restrict__ band_g, const double* __restrict__ Tw,
                        const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int ntiles_total,
                        int tiles_per_split, int h0, int w, double thr2d, const RansacState* __restrict__ state,
                        int32_t* __restrict__ pc, double* __restrict__ ps, float* __restrict__ dump, int dump_ld) {
-    constexpr int kColSplit = kEpiWarps / 8;
+    constexpr int kColSplit = kEpiWarps / (4 * kHT);
     constexpr int kColsPerThread = kRtTileN / kColSplit;
     constexpr int kChunks = kColsPerThread / 32;  // 32-column tcgen05.ld per thread and tile (even)
     constexpr int kEpiThreads = kEpiWarps * 32;
@@ -231,7 +231,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         tc::fence_barrier_init();
     }
     if (threadIdx.x < kHT * kRtTileM) { s_dsum[threadIdx.x] = 0.0; s_dcnt[threadIdx.x] = 0.0; }
-    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 512);
+    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 2 * kHT * kRtTileN);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -282,8 +282,8 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         }
     } else {
         // ===== epilogue: one thread per hypothesis row and column part =====
-        const int a = (warp >> 2) & 1;                     // A tile of this warp
-        const int half = warp >> 3;                        // column part of every tile this warp drains
+        const int a = (warp >> 2) % kHT;                   // A tile of this warp
+        const int half = warp / (4 * kHT);                 // column part of every tile this warp drains
         const int rloc = a * kRtTileM + (warp & 3) * 32 + lane;  // row inside the CTA
         const int j = jcta + rloc;                         // wave-relative hypothesis
         const bool valid = j < w;
@@ -435,7 +435,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, 512);
+    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, 2 * kHT * kRtTileN);
 }
 
 constexpr size_t kScoreSmem = kHT * kATileBytes + kStages * kBTileBytes + kListCap * sizeof(int2) +
@@ -452,7 +452,7 @@ void rt_split_plan(const cb_ctx* ctx, int m, int w, int* P, int* tiles_per_split
     for (int p = 1; p <= min(ntiles, 32); ++p) {
         const int tps = cb_div_up(ntiles, p);
         const int pp = cb_div_up(ntiles, tps);
-        const int rounds = cb_div_up(groups * pp, ctx->sm_count);
+        const int rounds = cb_div_up(groups * pp, ctx->sm_count * (kHT == 2 ? 1 : 2));  // resident CTAs per SM
         const double cost = rounds * (tps + 2.0);
         if (cost < best_cost - 1e-9) { best_cost = cost; best_p = p; }
     }
@@ -483,8 +483,8 @@ int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_b
     cudaError_t e;
     // the sum is streamed only when the caller asked for cb_ransac's per-hypothesis `sums`
     static const int epi_warps = [] {
-        const char* e = getenv("CB_RT_EPI_WARPS");  // tuning knob: 8 or 16 epilogue warps
-        return e && atoi(e) == 8 ? 8 : kMaxEpiWarps;
+        const char* e = getenv("CB_RT_EPI_WARPS");  // tuning knob: 8 or 16 epilogue warps (one CTA per SM only)
+        return kHT == 2 && e && atoi(e) == 8 ? 8 : kMaxEpiWarps;
     }();
     using kern_t = void (*)(const __nv_bfloat16*, const __nv_bfloat16*, const float*, const double*, const float4*,
                             const float4*, int, int, int, int, int, double, const RansacState*, int32_t*, double*, float*, int);
@@ -493,8 +493,8 @@ int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_b
         kern = dump ? ransac_tc_score_kernel<true, 32, true, 8>
                     : (want_sum ? ransac_tc_score_kernel<false, 64, true, 8> : ransac_tc_score_kernel<false, 64, false, 8>);
     else
-        kern = dump ? ransac_tc_score_kernel<true, 32, true, 16>
-                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, 16> : ransac_tc_score_kernel<false, 64, false, 16>);
+        kern = dump ? ransac_tc_score_kernel<true, 32, true, 8 * kHT>
+                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, 8 * kHT> : ransac_tc_score_kernel<false, 64, false, 8 * kHT>);
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
     if (e == cudaSuccess)
         kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), epi_warps * 32 + 64, kScoreSmem, st>>>(
