@@ -148,6 +148,27 @@ __device__ __forceinline__ double knn_exact_key_q64(const double* __restrict__ q
     return acc;
 }
 
+// ... and the candidate row staged 16-byte aligned in shared memory, read four columns at a time
+template <int D>
+__device__ __forceinline__ double knn_exact_key_q64_vec(const double* __restrict__ qd, const float* __restrict__ rp, int maxdot) {
+    double acc = 0.0;
+#pragma unroll
+    for (int c = 0; c < D; c += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(rp + c);
+        const float r4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (maxdot) {
+                acc = __dadd_rn(acc, __dmul_rn(qd[c + e], (double)r4[e]));
+            } else {
+                const double df = __dsub_rn(qd[c + e], (double)r4[e]);
+                acc = __dadd_rn(acc, __dmul_rn(df, df));
+            }
+        }
+    }
+    return maxdot ? -acc : acc;
+}
+
 __device__ __forceinline__ bool knn_less(double a, int ia, double b, int ib) {
     return a < b || (a == b && ia < ib);
 }
@@ -169,12 +190,17 @@ __device__ __forceinline__ double knn_unsortable(unsigned long long s) {
 }
 
 constexpr int kRowPad = 33;  // floats per staged row: lane l reading column c of row l hits bank (l + c) % 32
+constexpr int kRowVec = 36;  // ... or 16-byte aligned rows read with LDS.128: conflict-free per quarter-warp (36 l mod 32 = 4 l)
 
 // asynchronous 4-byte copy global -> shared (LDGSTS): the copies of a whole batch are in flight together;
 // with a register in between ptxas paired every load with its store and the rows arrived one L2
 // latency after the other (SASS, round 2)
 __device__ __forceinline__ void knn_cp_async4(float* dst_smem, const float* src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void knn_cp_async16(float* dst_smem, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
                  : "memory");
 }
 __device__ __forceinline__ void knn_cp_async_wait() {
@@ -198,15 +224,18 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
                   double gamma, const int32_t* __restrict__ unscramble, int unscramble_n,
                   int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist,
                   int32_t* __restrict__ fb_list, int* __restrict__ fb_count) {
-    __shared__ float s_rows[8][32][kRowPad];
-    __shared__ double s_q[8][32];
+    __shared__ __align__(16) float s_rows[8][32][kRowVec];
+    __shared__ __align__(16) double s_q[8][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int qi = blockIdx.x * (blockDim.x >> 5) + warp;
+    // rows of 16 or 32 floats at their natural stride: every lane copies ITS candidate's row with 16-byte
+    // asynchronous copies and reads it back with LDS.128 (stride 36: conflict-free per quarter-warp)
+    const bool vec = (d == 32 || d == 16) && dq_stride == d && ((size_t)r & 15) == 0;
     if (qi >= nq) return;
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int ncand = S * KC;
     const float* qp = q + (size_t)qi * dq_stride;
-    float (*rows)[kRowPad] = s_rows[warp];
+    float (*rows)[kRowVec] = s_rows[warp];
     s_q[warp][lane] = lane < d ? (double)qp[lane] : 0.0;
     unsigned long long key[SL];
     int id[SL];
@@ -222,19 +251,33 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
         key[t] = ~0ull;
         if (!__ballot_sync(0xffffffffu, j >= 0)) continue;
         __syncwarp();
+        if (vec) {
+            if (j >= 0) {
+                CB_DEV_CHECK(j < nr_total);
+                const float* src = r + (size_t)j * d;
+                if (d == 32) {
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4) knn_cp_async16(&rows[lane][c], src + c);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 16; c += 4) knn_cp_async16(&rows[lane][c], src + c);
+                }
+            }
+        } else {
 #pragma unroll 8
-        for (int rr = 0; rr < 32; ++rr) {
-            const int jj = __shfl_sync(0xffffffffu, j, rr);
-            CB_DEV_CHECK(jj < nr_total);
-            if (jj >= 0 && lane < d) knn_cp_async4(&rows[rr][lane], r + (size_t)jj * dq_stride + lane);
+            for (int rr = 0; rr < 32; ++rr) {
+                const int jj = __shfl_sync(0xffffffffu, j, rr);
+                CB_DEV_CHECK(jj < nr_total);
+                if (jj >= 0 && lane < d) knn_cp_async4(&rows[rr][lane], r + (size_t)jj * dq_stride + lane);
+            }
         }
         knn_cp_async_wait();
         __syncwarp();
         if (j >= 0) {
             id[t] = j;
-            const double kd = d == 32 ? knn_exact_key_q64<32>(s_q[warp], rows[lane], d, maxdot)
-                                      : (d == 16 ? knn_exact_key_q64<16>(s_q[warp], rows[lane], d, maxdot)
-                                                 : knn_exact_key_q64<0>(s_q[warp], rows[lane], d, maxdot));
+            const double kd = vec ? (d == 32 ? knn_exact_key_q64_vec<32>(s_q[warp], rows[lane], maxdot)
+                                             : knn_exact_key_q64_vec<16>(s_q[warp], rows[lane], maxdot))
+                                  : knn_exact_key_q64<0>(s_q[warp], rows[lane], d, maxdot);
             key[t] = knn_sortable(kd);
         }
     }
