@@ -470,10 +470,27 @@ def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, m
     symmetry.sym_pose_many(c5[:2], workers=1)
     torch.cuda.synchronize()
     ms_seq = 1e3 * (time.perf_counter() - t0) / 2
+    # per-class device time of the same two pairs (one stream, CUDA events inside the library) -> roofline of
+    # the scoring kernel at this shape (M = 250 000, H = 4 096 per RANSAC) and the classes' shares
+    ctx.timing_reset()
+    ctx.timing(True)
+    symmetry.sym_pose_many(c5[:2], workers=1)
+    ctx.timing(False)
+    cls = ctx.timing_read()
+    sc_ms, sc_evals, _ = cls["ransac_score"]
+    tot_ms = sum(v[0] for k, v in cls.items() if k != "ransac_waves")
+    c5_roof = {"bound": "tensor", "kernel": "ransac_tc_score_kernel", "unit": "TFLOP/s", "peak": peaks["bf16_burst"],
+               "achieved": sc_evals / max(sc_ms, 1e-9) * 1e3 * 2.0 * ctx.ransac_k() / 1e12,
+               "evals_per_s": sc_evals / max(sc_ms, 1e-9) * 1e3,
+               "kernel_class_share_of_tracked": {k: round(v[0] / max(tot_ms, 1e-9), 4) for k, v in cls.items()
+                                                 if k != "ransac_waves" and v[2] > 0},
+               "note": "issued bf16 flop of the scoring launches of two pairs registered one after the other; peak = "
+                       f"{peaks['src']} bf16 dense burst"}
+    c5_roof["frac"] = c5_roof["achieved"] / c5_roof["peak"]
     regs = [1 + (8 if j[0][4] >= 2 else 2) for j in c5]
     out["c5"] = {"value": world * n_c5 / (ms * 1e-3), "unit": "pairs/s", "pairs_per_rank": n_c5, "ms": ms,
                  "sequential_ms_per_pair": ms_seq, "registrations_per_pair": regs,
-                 "symmetry_ok": [bool(r[4]) for r in res],
+                 "symmetry_ok": [bool(r[4]) for r in res], "roofline": c5_roof,
                  "workload": "C5: table, 50 000-point scan vs 10 000-point CAD (M = 250 000), 4096 hypotheses per RANSAC, pos_sym "
                              "drawn from the real label histogram (K = 4 and nine registrations when >= 2), device-resident"}
 

@@ -29,12 +29,21 @@
 namespace {
 
 constexpr int kHT = kRtHT;        // A tiles (of 128 hypotheses) per CTA
-constexpr int kStages = kHT == 2 ? 6 : 3;  // shared-memory ring of 24 KB B tiles
+// "phased" epilogue (needs kHT == 1): one CTA of 128 hypotheses per SM, FOUR 128-column accumulator
+// stages; epilogue warp group g = warp / 4 drains the whole tiles t = g (mod 4), so the MMA warp can run
+// up to four tiles ahead and no warp waits for the slowest of the sixteen
+#ifndef CB_RT_PHASED
+#define CB_RT_PHASED 0
+#endif
+constexpr bool kPhased = CB_RT_PHASED != 0;
+static_assert(!kPhased || kHT == 1, "the phased epilogue drains one A tile per CTA");
+constexpr int kTS = kPhased ? 4 : 2;  // tensor-memory accumulator stages
+constexpr int kStages = (kHT == 2 || kPhased) ? 6 : 3;  // shared-memory ring of 24 KB B tiles
 // epilogue warps: 4 lane quadrants x kHT A tiles x (EW / (4 kHT)) column parts.  16 (four per SM sub-partition)
 // is the default: with 8 the kernel was bound by the epilogue's dependent-issue latency (ncu, round 2:
 // issue active 48 %, tensor pipe 49 %, warps active 15.6 %, stall `wait` 1.0 per issue)
-constexpr int kMaxEpiWarps = 8 * kHT;
-constexpr int kListCap = kHT == 2 ? 2048 : 1024;  // queued in-band evaluations per CTA (overflow is settled inline)
+constexpr int kMaxEpiWarps = kPhased ? 16 : 8 * kHT;
+constexpr int kListCap = (kHT == 2 || kPhased) ? 2048 : 1024;  // queued in-band evaluations per CTA (overflow is settled inline)
 constexpr int kListDrain = kListCap / 2;          // drain the queue at the next tile boundary once it holds this many
 constexpr uint32_t kATileBytes = kRtTileM * kRtKP * 2;  // 24 KB
 constexpr uint32_t kBTileBytes = kRtTileN * kRtKP * 2;  // 24 KB
@@ -102,7 +111,7 @@ ransac_tc_pack_corr_kernel(const float4* __restrict__ src4, const float4* __rest
 
 // ------------------------------------------------------------------------------ scoring
 struct RtCtl {
-    uint64_t a_full, full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+    uint64_t a_full, full[kStages], empty[kStages], tmem_full[4], tmem_empty[4];
     uint32_t tmem_base;
     int list_n;
 };
@@ -192,13 +201,13 @@ __device__ __forceinline__ void rt_drain(RtCtl* ctl, const int2* list, double* s
 }
 
 template <bool DUMP, int LDW, bool WSUM, int kEpiWarps>
-__global__ void __launch_bounds__(kEpiWarps * 32 + 64, kHT == 2 ? 1 : 2)
+__global__ void __launch_bounds__(kEpiWarps * 32 + 64, (kHT == 2 || kPhased) ? 1 : 2)
 ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloat16* __restrict__ Bpack,
                        const float* __restrict__ band_g, const double* __restrict__ Tw,
                        const float4* __restrict__ src4, const float4* __restrict__ tgt4, int m, int ntiles_total,
                        int tiles_per_split, int h0, int w, double thr2d, const RansacState* __restrict__ state,
                        int32_t* __restrict__ pc, double* __restrict__ ps, float* __restrict__ dump, int dump_ld) {
-    constexpr int kColSplit = kEpiWarps / (4 * kHT);
+    constexpr int kColSplit = kPhased ? 1 : kEpiWarps / (4 * kHT);
     constexpr int kColsPerThread = kRtTileN / kColSplit;
     constexpr int kChunks = kColsPerThread / 32;  // 32-column tcgen05.ld per thread and tile (even)
     constexpr int kEpiThreads = kEpiWarps * 32;
@@ -223,15 +232,15 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
             tc::mbar_init(&ctl->full[i], 1);
             tc::mbar_init(&ctl->empty[i], 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kTS; ++i) {
             tc::mbar_init(&ctl->tmem_full[i], 1);
-            tc::mbar_init(&ctl->tmem_empty[i], kEpiWarps);
+            tc::mbar_init(&ctl->tmem_empty[i], kPhased ? 4 : kEpiWarps);
         }
         ctl->list_n = 0;
         tc::fence_barrier_init();
     }
     if (threadIdx.x < kHT * kRtTileM) { s_dsum[threadIdx.x] = 0.0; s_dcnt[threadIdx.x] = 0.0; }
-    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, 2 * kHT * kRtTileN);
+    if (warp == kEpiWarps) tc::tmem_alloc(&ctl->tmem_base, kTS * kHT * kRtTileN);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -260,7 +269,7 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         tc::mbar_wait(&ctl->a_full, 0);
         for (int it = 0; it < ntiles; ++it) {
             const int st = it % kStages, use = it / kStages;
-            const int ts = it & 1, tuse = it >> 1;
+            const int ts = it % kTS, tuse = it / kTS;
             tc::mbar_wait(&ctl->full[st], use & 1);
             tc::mbar_wait(&ctl->tmem_empty[ts], (tuse & 1) ^ 1);
             tc::fence_after_sync();
@@ -282,8 +291,10 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         }
     } else {
         // ===== epilogue: one thread per hypothesis row and column part =====
-        const int a = (warp >> 2) % kHT;                   // A tile of this warp
-        const int half = warp / (4 * kHT);                 // column part of every tile this warp drains
+        const int a = kPhased ? 0 : (warp >> 2) % kHT;     // A tile of this warp
+        const int half = kPhased ? 0 : warp / (4 * kHT);   // column part of every tile this warp drains
+        const int group = warp >> 2;                       // phased: this warp drains the tiles t = group (mod 4)
+        const bool first = kPhased ? group == 0 : half == 0;  // the thread of a row that adds the queue's corrections
         const int rloc = a * kRtTileM + (warp & 3) * 32 + lane;  // row inside the CTA
         const int j = jcta + rloc;                         // wave-relative hypothesis
         const bool valid = j < w;
@@ -338,7 +349,50 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         };
         constexpr bool kPipelined = LDW == 64 && kChunks == 4;
         constexpr bool kBoth = LDW == 64 && kChunks == 2;  // 16 warps: the thread's 64 columns in two loads, one wait
-        float va[kPipelined || kBoth ? 64 : 1], vb[kPipelined ? 64 : 1];
+        float va[kPipelined || kBoth || kPhased ? 64 : 1], vb[kPipelined ? 64 : 1];
+        if constexpr (kPhased) {
+            const int n_iter = (ntiles + 3) >> 2;
+            for (int k = 0; k < n_iter; ++k) {
+                const int it = 4 * k + group;
+                if (it < ntiles) {
+                    tc::mbar_wait(&ctl->tmem_full[group], k & 1);
+                    tc::fence_after_sync();
+                    const int col0 = (t0 + it) * kRtTileN;
+                    const uint32_t taddr = lane_addr + group * kRtTileN;
+                    s2 = pk2(0.f, 0.f);
+                    c2 = pk2(0.f, 0.f);
+                    tc::tmem_ld32(taddr, va);
+                    tc::tmem_ld32(taddr + 32, va + 32);
+                    tc::tmem_ld_wait64(va);
+                    process(*reinterpret_cast<const float(*)[32]>(va), col0);
+                    process(*reinterpret_cast<const float(*)[32]>(va + 32), col0 + 32);
+                    tc::tmem_ld32(taddr + 64, va);
+                    tc::tmem_ld32(taddr + 96, va + 32);
+                    tc::tmem_ld_wait64(va);
+                    tc::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(&ctl->tmem_empty[group]);
+                    process(*reinterpret_cast<const float(*)[32]>(va), col0 + 64);
+                    process(*reinterpret_cast<const float(*)[32]>(va + 32), col0 + 96);
+                    float x, y;
+                    unpk2(c2, x, y);  // at most 64 per tile: exact in fp32
+                    cnt_i += (unsigned)(x + y);
+                    if (WSUM) {
+                        unpk2(s2, x, y);
+                        sum_d += (double)x + (double)y;
+                    }
+                }
+                // every 16 tiles: if the queue is half full (a CTA-uniform decision) drain it
+                if ((k & 3) != 3) continue;
+                named_bar_sync(1, kEpiThreads);
+                if (*(volatile int*)&ctl->list_n >= kListDrain) {
+                    rt_drain<kEpiThreads>(ctl, list, s_dcnt, s_dsum, jcta, w, Tw, src4, tgt4, thr2d);
+                    named_bar_sync(1, kEpiThreads);
+                    if (threadIdx.x == 0) ctl->list_n = 0;
+                    named_bar_sync(1, kEpiThreads);
+                }
+            }
+        } else
         for (int it = 0; it < ntiles; ++it) {
             const int ts = it & 1, tuse = it >> 1;
             tc::mbar_wait(&ctl->tmem_full[ts], tuse & 1);
@@ -425,17 +479,17 @@ ransac_tc_score_kernel(const __nv_bfloat16* __restrict__ Apack, const __nv_bfloa
         named_bar_sync(1, kEpiThreads);
         if (valid) {
             // this thread's share of the row; the queue's corrections ride with the first half
-            const double c = (double)cnt_i + dcnt + (half == 0 ? s_dcnt[rloc] : 0.0);
+            const double c = (double)cnt_i + dcnt + (first ? s_dcnt[rloc] : 0.0);
             const long long ci = llrint(c);
             // totals over column halves and correspondence splits (zeroed by the fit kernel)
             atomicAdd(&pc[j], (int)ci);
             // sum of squared inlier distances = sum (d^2 - thr^2) + count * thr^2
-            if (WSUM) atomicAdd(&ps[j], sum_d + dsum + (half == 0 ? s_dsum[rloc] : 0.0) + (double)ci * thr2d);
+            if (WSUM) atomicAdd(&ps[j], sum_d + dsum + (first ? s_dsum[rloc] : 0.0) + (double)ci * thr2d);
         }
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, 2 * kHT * kRtTileN);
+    if (warp == kEpiWarps) tc::tmem_dealloc(tbase, kTS * kHT * kRtTileN);
 }
 
 constexpr size_t kScoreSmem = kHT * kATileBytes + kStages * kBTileBytes + kListCap * sizeof(int2) +
@@ -452,7 +506,7 @@ void rt_split_plan(const cb_ctx* ctx, int m, int w, int* P, int* tiles_per_split
     for (int p = 1; p <= min(ntiles, 32); ++p) {
         const int tps = cb_div_up(ntiles, p);
         const int pp = cb_div_up(ntiles, tps);
-        const int rounds = cb_div_up(groups * pp, ctx->sm_count * (kHT == 2 ? 1 : 2));  // resident CTAs per SM
+        const int rounds = cb_div_up(groups * pp, ctx->sm_count * ((kHT == 2 || kPhased) ? 1 : 2));  // resident CTAs per SM
         const double cost = rounds * (tps + 2.0);
         if (cost < best_cost - 1e-9) { best_cost = cost; best_p = p; }
     }
@@ -493,8 +547,8 @@ int ransac_tc_score_launch(cb_ctx* ctx, const __nv_bfloat16* Apack, const __nv_b
         kern = dump ? ransac_tc_score_kernel<true, 32, true, 8>
                     : (want_sum ? ransac_tc_score_kernel<false, 64, true, 8> : ransac_tc_score_kernel<false, 64, false, 8>);
     else
-        kern = dump ? ransac_tc_score_kernel<true, 32, true, 8 * kHT>
-                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, 8 * kHT> : ransac_tc_score_kernel<false, 64, false, 8 * kHT>);
+        kern = dump ? ransac_tc_score_kernel<true, 32, true, kMaxEpiWarps>
+                    : (want_sum ? ransac_tc_score_kernel<false, 64, true, kMaxEpiWarps> : ransac_tc_score_kernel<false, 64, false, kMaxEpiWarps>);
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScoreSmem);
     if (e == cudaSuccess)
         kern<<<dim3(cb_div_up(w, kHT * kRtTileM), P), epi_warps * 32 + 64, kScoreSmem, st>>>(
