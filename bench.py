@@ -151,6 +151,14 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+def base_config(args, sweep):
+    """The workload description both arms print (same keys, same values)."""
+    return {"workload": WORKLOAD, "db": L_DB, "descriptor_dim": D_DESC, "feature_dim": args.feature_dim, "k_nn": K_NN,
+            "pairs_per_step_per_rank": PAIRS_PER_STEP,
+            "ransac": "budget 100000, adaptive stop (confidence 0.999), ransac_n 10, max_corr 0.2",
+            "points_per_cloud_after_0.03_dedup": sweep.point_counts(), "cad_pool": CAD_POOL}
+
+
 # ------------------------------------------------------------------------------------ CPU arm
 def cpu_pair(q, cad):
     """One registered pair on the CPU: the oracle's restatement of sym_pose (reference Python
@@ -205,7 +213,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "query-CAD pairs registered/sec", "value": v, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "feature_dim": args.feature_dim, "sample": sample},
+        "config": dict(base_config(args, sweep), sample=sample),
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -393,13 +401,10 @@ def run_ours(args, rank, world, local_rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 search / f64 re-rank, fit and in-band scoring",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "db": L_DB, "descriptor_dim": D_DESC, "feature_dim": args.feature_dim, "k_nn": K_NN,
-                   "pairs_per_step_per_rank": PAIRS_PER_STEP, "pairs_timed": pairs,
-                   "ransac": "budget 100000, adaptive stop (confidence 0.999), ransac_n 10, max_corr 0.2",
-                   "points_per_cloud_after_0.03_dedup": sweep.point_counts(), "cad_pool": CAD_POOL,
-                   "l2": "256 MiB flush between timed steps", "driver": symmetry.driver_name(), "concurrency": workers,
-                   "sequential_ms_per_pair": ms_seq_pair,
-                   "sharding": f"queries sharded over {world} rank(s), no data-path collective"},
+        "config": dict(base_config(args, sweep), **{
+            "pairs_timed": pairs, "l2": "256 MiB flush between timed steps", "driver": symmetry.driver_name(),
+            "concurrency": workers, "sequential_ms_per_pair": ms_seq_pair,
+            "sharding": f"queries sharded over {world} rank(s), no data-path collective"}),
         "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d_step,
                 "d2h_bytes_per_step": d2h_step, "bytes": "counted where the copies are made (Context.dev / Context.host / "
                                                            "the library's own staging), averaged over warm-up + timed steps"},
