@@ -341,6 +341,27 @@ def run_ours(args, rank, world, local_rank):
                "ms_per_step": ms16 / n16, "workload": "the C3 sweep with 16-d per-point features (evaluation.py:183), device-resident"}
         del s16
 
+    # (4) strong scaling: ONE fixed sweep of 8 steps (800 pairs, the same on every run) split over the ranks
+    #     (rank r registers steps r, r + N, ...); the headline above is weak scaling (fixed sweep per rank)
+    strong = None
+    if not args.quick:
+        fixed = Sweep(424242, args.feature_dim, 8).to(up)
+        mine = [fixed.steps[i] for i in range(rank, 8, world)]
+        for st_ in mine[:1]:
+            gpu_step(retrieval, symmetry, fixed, st_, workers)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for st_ in mine:
+            gpu_step(retrieval, symmetry, fixed, st_, workers)
+        e1.record()
+        barrier()
+        ms_fix = max_over_ranks(e0.elapsed_time(e1))
+        strong = {"value": 8 * PAIRS_PER_STEP / (ms_fix * 1e-3), "unit": "pairs/s", "ms": ms_fix, "pairs": 8 * PAIRS_PER_STEP,
+                  "scaling": "strong", "workload": "one fixed C3 sweep of 800 pairs (8 steps, the same at every N) split over the "
+                                                   "ranks step by step, device-resident, max over ranks"}
+        del fixed
+
     extra = {} if args.quick else side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, max_over_ranks)
     if rank != 0:
         return
@@ -409,7 +430,7 @@ def run_ours(args, rank, world, local_rank):
                 "d2h_bytes_per_step": d2h_step, "bytes": "counted where the copies are made (Context.dev / Context.host / "
                                                            "the library's own staging), averaged over warm-up + timed steps"},
         "gpu_launches": launches_per_step * args.steps, "launches_per_pair": launches_per_step / PAIRS_PER_STEP,
-        "roofline": roof, "kernel_classes": shares, "d16": d16, **extra,
+        "roofline": roof, "kernel_classes": shares, "d16": d16, "strong": strong, **extra,
         "cpu_baseline": cpu_base, "clocks": clocks}))
 
 

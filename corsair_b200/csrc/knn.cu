@@ -337,10 +337,17 @@ knn_rerank_kernel(const float* __restrict__ q, int nq, const float* __restrict__
 // keeps its own k best in registers (sorted, k <= 12 in engine E1); the block then merges the 256
 // sorted lists in k rounds of "smallest head".  (Round 1 rescanned all references once per round, every
 // thread walking its own global rows: 900 us for a single queued row at 50 000 x 10 000.)
+// With few queued rows (the usual case: 0-2) one block per row leaves the row's 40 x 256-reference steps
+// on a single SM, ~50-100 us of pure latency; the references of a row are therefore split over up to
+// kFbParts blocks (part p scans the steps t = p mod parts), each writes its k best to a scratch list and
+// the last part to finish (atomic ticket) merges them.
 constexpr int kFbK = 12;
+constexpr int kFbParts = 8;
+constexpr int kFbSplitRows = 1024;  // rows the scratch lists hold; more queued rows run one block per row
 __global__ void __launch_bounds__(256)
 knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, int nr, int d, int stride,
                     int k, int metric, const int32_t* __restrict__ fb_list, const int* __restrict__ fb_count,
+                    unsigned long long* __restrict__ part_key, int* __restrict__ part_idx, int* __restrict__ part_done,
                     int64_t* __restrict__ idx64, int32_t* __restrict__ idx32, float* __restrict__ dist) {
     __shared__ float s_rows[256][kRowPad];
     __shared__ float s_q[32];
@@ -351,7 +358,11 @@ knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, in
     const int maxdot = metric == CB_KNN_MAXDOT;
     const int n = *fb_count;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int e = blockIdx.x; e < n; e += gridDim.x) {
+    __shared__ int s_last;
+    const int steps = (nr + 255) / 256;
+    const int parts = (n > 0 && n <= kFbSplitRows) ? max(1, min(min(kFbParts, steps), (int)gridDim.x / n)) : 1;
+    for (int u = blockIdx.x; u < n * parts; u += gridDim.x) {
+        const int e = u / parts, part = u % parts;
         const int qi = fb_list[e];
         __syncthreads();
         if (threadIdx.x < 32) s_q[threadIdx.x] = threadIdx.x < d ? q[(size_t)qi * stride + threadIdx.x] : 0.f;
@@ -359,7 +370,7 @@ knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, in
         int bj[kFbK];
 #pragma unroll
         for (int t = 0; t < kFbK; ++t) { bk[t] = ~0ull; bj[t] = 0x7fffffff; }
-        for (int base = 0; base < nr; base += 256) {
+        for (int base = part * 256; base < nr; base += parts * 256) {
             const int nt = min(256, nr - base);
             __syncthreads();
             // warp w copies rows w, w + 8, ...: one coalesced load per row
@@ -401,7 +412,10 @@ knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, in
                     if (s_key[w] < wk || (s_key[w] == wk && s_id[w] < wi)) { wk = s_key[w]; wi = s_id[w]; }
                 s_wkey = wk;
                 s_wid = wi;
-                if (wi != 0x7fffffff) {
+                if (parts > 1) {
+                    part_key[((size_t)e * kFbParts + part) * kFbK + round] = wk;
+                    part_idx[((size_t)e * kFbParts + part) * kFbK + round] = wi;
+                } else if (wi != 0x7fffffff) {
                     const size_t o = (size_t)qi * k + round;
                     if (idx64) idx64[o] = wi;
                     if (idx32) idx32[o] = wi;
@@ -415,6 +429,53 @@ knn_fallback_kernel(const float* __restrict__ q, const float* __restrict__ r, in
                 for (int t = 0; t + 1 < kFbK; ++t) { bk[t] = bk[t + 1]; bj[t] = bj[t + 1]; }
                 bk[kFbK - 1] = ~0ull;
                 bj[kFbK - 1] = 0x7fffffff;
+            }
+        }
+        if (parts > 1) {
+            // the last part of this row to finish merges the parts' sorted lists (warp 0: <= 96 entries, three
+            // per lane, k rounds of three REDUX minima)
+            if (threadIdx.x == 0) {
+                __threadfence();
+                s_last = atomicAdd(&part_done[e], 1) == parts - 1;
+            }
+            __syncthreads();
+            if (s_last && warp == 0) {
+                __threadfence();
+                unsigned long long mk[3];
+                int mj[3];
+#pragma unroll
+                for (int t = 0; t < 3; ++t) {
+                    const int i = lane + 32 * t;  // entry (part i / k, round i % k)
+                    const bool ok = i < parts * k;
+                    const size_t o = ((size_t)e * kFbParts + (ok ? i / k : 0)) * kFbK + (ok ? i % k : 0);
+                    mk[t] = ok ? __ldcg(&part_key[o]) : ~0ull;
+                    mj[t] = ok ? __ldcg(&part_idx[o]) : 0x7fffffff;
+                }
+                for (int round = 0; round < k; ++round) {
+                    unsigned long long b = ~0ull;
+                    int bi = 0x7fffffff;
+#pragma unroll
+                    for (int t = 0; t < 3; ++t)
+                        if (mk[t] < b || (mk[t] == b && mj[t] < bi)) { b = mk[t]; bi = mj[t]; }
+                    const unsigned hi = (unsigned)(b >> 32), lo = (unsigned)b;
+                    const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+                    const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+                    const bool tied = hi == mh && lo == ml;
+                    const int wi = (int)__reduce_min_sync(0xffffffffu, tied ? (unsigned)bi : 0x7fffffffu);
+                    if (wi == 0x7fffffff) break;
+                    if (tied && bi == wi) {
+#pragma unroll
+                        for (int t = 0; t < 3; ++t)
+                            if (mj[t] == wi) { mk[t] = ~0ull; mj[t] = 0x7fffffff; }
+                    }
+                    if (lane == 0) {
+                        const size_t o = (size_t)qi * k + round;
+                        if (idx64) idx64[o] = wi;
+                        if (idx32) idx32[o] = wi;
+                        if (dist) dist[o] = knn_out_dist(knn_unsortable(((unsigned long long)mh << 32) | ml), metric);
+                    }
+                }
+                if (lane == 0) part_done[e] = 0;
             }
         }
     }
@@ -484,8 +545,14 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
     int32_t* ci = cb_alloc_t<int32_t>(ctx, (size_t)nq * S * LC);
     float* bound = cb_alloc_t<float>(ctx, (size_t)nq * S);
     int32_t* fb = cb_alloc_t<int32_t>(ctx, nq);
-    if (!scal || !ci || !bound || !fb) return CB_ENOMEM;
+    // scratch of the exact fallback's split rows: per row and part kFbK (key, index) entries, a ticket per row
+    const size_t fb_entries = (size_t)kFbSplitRows * kFbParts * kFbK;
+    unsigned long long* fb_key = cb_alloc_t<unsigned long long>(ctx, fb_entries);
+    int* fb_idx = cb_alloc_t<int>(ctx, fb_entries);
+    int* fb_done = cb_alloc_t<int>(ctx, kFbSplitRows);
+    if (!scal || !ci || !bound || !fb || !fb_key || !fb_idx || !fb_done) return CB_ENOMEM;
     CB_CUDA(ctx, cudaMemsetAsync(scal, 0, 2 * sizeof(unsigned int), st));
+    CB_CUDA(ctx, cudaMemsetAsync(fb_done, 0, kFbSplitRows * sizeof(int), st));
     ctx->knn_fb_count = (const int*)(scal + 1);
     const int maxdot = metric == CB_KNN_MAXDOT;
     double gamma = (dp + 4) * 6.0e-8;
@@ -535,8 +602,9 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
                                                scal, gamma, unscramble, cb_div_up(nr, 256) * 256, idx, idx32, dist, fb, (int*)(scal + 1));
         CB_LAUNCH_CHECK(ctx);
     }
-    knn_fallback_kernel<<<min(nq, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, stride, k, metric, fb,
-                                                                     (int*)(scal + 1), idx, idx32, dist);
+    knn_fallback_kernel<<<min(nq * kFbParts, 4 * ctx->sm_count), 256, 0, st>>>(qd, rd, nr, d, stride, k, metric, fb,
+                                                                                (int*)(scal + 1), fb_key, fb_idx, fb_done,
+                                                                                idx, idx32, dist);
     CB_LAUNCH_CHECK(ctx);
     return CB_OK;
 }
@@ -549,7 +617,7 @@ static size_t knn_workspace(cb_ctx* ctx, int nq, int nr, int d, int k) {
     b += cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nr * 32 * 4);  // pads
     b += cb_align((size_t)nr * 4) + 256;
     b += 2 * cb_align((size_t)nq * 256 * 4) + cb_align((size_t)nq * 32 * 4) + cb_align((size_t)nq * 4);
-    b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + cb_align((size_t)(nr + 256) * 4) + (1 << 16);  // packed bf16 operand tiles + un-scramble table of the tc variant
+    b += cb_align((size_t)(nq + 128) * 112 * 2) + cb_align((size_t)(nr + 256) * 112 * 2) + cb_align((size_t)(nr + 256) * 4) + (size_t)kFbSplitRows * (kFbParts * kFbK * 12 + 4) + (1 << 16);  // packed bf16 operand tiles + un-scramble table of the tc variant
     return b;
 }
 

@@ -16,9 +16,10 @@ def main():
         shapes = [tuple(int(x) for x in a.split("x")) for a in sys.argv[1:]]
     ctx = get_context(0)
     rng = np.random.default_rng(0)
+    D = int(os.environ.get("KNN_D", "32"))  # feature width
     for n0, n1 in shapes:
-        F0 = rng.standard_normal((n0, 32)).astype(np.float32)
-        F1 = rng.standard_normal((n1, 32)).astype(np.float32)
+        F0 = rng.standard_normal((n0, D)).astype(np.float32)
+        F1 = rng.standard_normal((n1, D)).astype(np.float32)
         F0 /= np.linalg.norm(F0, axis=1, keepdims=True)
         F1 /= np.linalg.norm(F1, axis=1, keepdims=True)
         a, b = torch.from_numpy(F0).cuda(), torch.from_numpy(F1).cuda()
@@ -33,7 +34,7 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) / reps * 1e3
-        print(f"knn {n0} x {n1} (D=32, k=5): {us:.1f} us per call, {2.0 * n0 * n1 * 32 / us / 1e6:.1f} TFLOP/s algorithmic, "
+        print(f"knn {n0} x {n1} (D={D}, k=5): {us:.1f} us per call, {2.0 * n0 * n1 * D / us / 1e6:.1f} TFLOP/s algorithmic, "
               f"fallback rows {ctx.knn_last_fallback_rows()}")
 
 

@@ -56,3 +56,23 @@ def test_knn_quoted_shape_50000_x_10000(ctx, d, k):
         assert (np.sort(full, axis=1)[:, 1:] != np.sort(full, axis=1)[:, :-1]).all()
     # k <= 12 runs the tensor-core candidate pass: only genuine near-ties may need the exact fallback
     assert 0 <= fb <= 50000 // 200, f"{fb} of 50000 rows needed the exact fallback"
+
+
+@pytest.mark.parametrize("n0,n1,copies", [(40, 3000, 100), (700, 5000, 60), (2000, 1300, 80)])
+def test_knn_exact_fallback_rows_split_over_blocks(ctx, n0, n1, copies):
+    """Rows the candidate lists cannot prove (here: every reference exists `copies` times, so more
+    references tie at the threshold than a list holds) go to the exact brute-force kernel, whose rows are
+    split over several blocks when few are queued and merged by the last block to finish: the answer is
+    still the oracle's (distance, index) order, and the test asserts that the fallback really ran."""
+    from corsair_b200 import find_nn
+    rng = np.random.default_rng(n0 + n1)
+    base = unit_features(rng, n1 // copies, 32)
+    F1 = np.tile(base, (copies, 1))[:n1].copy()
+    F0 = unit_features(rng, n0, 32)
+    for k in (1, 5, 12):
+        idx, dist = find_nn.knn_device(F0, F1, k, return_distance=True)
+        fb = ctx.knn_last_fallback_rows()
+        ref_idx, ref_d2 = port.find_knn_exact(F0, F1, k)
+        assert np.array_equal(idx.cpu().numpy(), ref_idx)
+        np.testing.assert_allclose(dist.cpu().numpy(), ref_d2, rtol=1e-6, atol=1e-12)
+        assert fb > 0, "this input is built to overflow the candidate lists"
