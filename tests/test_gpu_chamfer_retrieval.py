@@ -64,7 +64,7 @@ def descriptors(rng, n, d=256):
     return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
 
 
-@pytest.mark.parametrize("Q,L", [(1, 6778), (993, 652), (64, 830)])
+@pytest.mark.parametrize("Q,L", [(1, 6778), (993, 652), (64, 830), (1000, 6778), (1000, 8436), (291, 830)])
 def test_retrieval_matches_cdist_argsort(ctx, rng, Q, L):
     from corsair_b200 import retrieval
     from scipy.spatial.distance import cdist

@@ -35,7 +35,8 @@ def variant(request, ctx):
 
 
 @pytest.mark.parametrize("M,H,thr", [(13000, 64, 0.2), (5003, 4096, 0.2), (50000, 4096, 0.4), (999, 1, 0.2),
-                                     (34145, 9000, 0.2), (127, 300, 0.2), (128, 256, 0.3), (250000, 512, 0.2)])
+                                     (34145, 9000, 0.2), (127, 300, 0.2), (128, 256, 0.3), (250000, 512, 0.2),
+                                     (13000, 100000, 0.2), (250000, 4096, 0.2)])  # the reference budget; C5
 def test_counts_bit_exact_fixed_sets(ctx, rng, variant, M, H, thr):
     from corsair_b200 import eval_pose
     src, tgt, _, _ = make_problem(rng, M)
