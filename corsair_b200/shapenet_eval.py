@@ -20,7 +20,6 @@ from ._capi import ptr
 from .eval_pose import eval_pose
 from .symmetry import sym_pose
 
-_worker_tls = __import__("threading").local()  # per-thread CUDA stream of register_many's workers
 
 SYM_ORDERS = (12, 8, 6, 4, 3, 2, 1)  # evaluation-shapenet.py:151 (1 = no symmetry)
 
@@ -138,38 +137,29 @@ def registration_worker(feats_pc, feats_pc_transformed, coords_pc, pc_quant, pc_
                 rte_sym=rte_sym, rre_sym=rre_sym, rte_ransac=rte_ransac, rre_ransac=rre_ransac)
 
 
-_pool = None
-_pool_workers = 0
-
-
-def register_many(items, workers=5, **kwargs):
+def register_many(items, workers=8, **kwargs):
     """The ``Parallel(n_jobs=-1)(delayed(self.registration_worker)(*x) for x in producer)`` loop of
-    evaluation-shapenet.py:341-343 on ``workers`` host threads (own cb_ctx + CUDA stream each, see
-    symmetry.sym_pose_many).  ``items``: iterable of the producer's 6-tuples; keywords go to
-    registration_worker; ``rng`` defaults to the int ``seed`` so that results do not depend on the
-    thread schedule.  Results in item order."""
-    global _pool, _pool_workers
+    evaluation-shapenet.py:341-343 without host threads: the symmetry labels of all items first (one
+    cb_self_hausdorff call each), then ONE symmetry.sym_pose_many call that keeps ``workers`` pairs in
+    flight (cb_sym_pose_many), then eval_pose of both poses per item.  ``items``: iterable of the
+    producer's 6-tuples; keywords as registration_worker; ``rng`` defaults to the int ``seed`` so that
+    every pair's segmentation draws are its own (an explicit RandomState keeps the sequential loop).
+    Results equal registration_worker's, in item order."""
+    from .symmetry import sym_pose_many
     kwargs.setdefault("rng", int(kwargs.get("seed", 0)))
     items = list(items)
-    if workers <= 1 or len(items) <= 1:
+    if workers <= 1 or len(items) <= 1 or not isinstance(kwargs["rng"], (int, np.integer)):
         return [registration_worker(*x, **kwargs) for x in items]
-    if _pool is None or _pool_workers != workers:
-        from concurrent.futures import ThreadPoolExecutor
-        if _pool is not None:
-            _pool.shutdown(wait=True)
-        _pool = ThreadPoolExecutor(max_workers=workers, thread_name_prefix="corsair_b200_shapenet")
-        _pool_workers = workers
-    device = torch.cuda.current_device()
-    ready = torch.cuda.Event()
-    ready.record(torch.cuda.current_stream(device))  # inputs may have been produced on the caller's stream
-
-    def run(x):
-        torch.cuda.set_device(device)
-        st = getattr(_worker_tls, "stream", None)
-        if st is None:
-            st = _worker_tls.stream = torch.cuda.Stream(device=device)
-        with torch.cuda.stream(st):
-            st.wait_event(ready)
-            return registration_worker(*x, **kwargs)
-
-    return list(_pool.map(run, items))
+    k_nn, max_corr = kwargs.get("k_nn", 5), kwargs.get("max_corr", 0.4)
+    seed, cd_threshold = kwargs.get("seed", 0), kwargs.get("cd_threshold", 0.1)
+    labels = [get_symmetry_label(x[2], cd_threshold) for x in items]
+    jobs = [((x[0], x[3], x[1], x[4], lab), dict(k_nn=k_nn, max_corr=max_corr, seed=seed, rng=int(kwargs["rng"])))
+            for x, lab in zip(items, labels)]
+    out = []
+    for x, lab, (T_sym, ch_sym, T_r, ch_r, ok) in zip(items, labels, sym_pose_many(jobs, workers=workers)):
+        rte_sym, rre_sym = eval_pose(T_sym, np.eye(4), x[5], axis_symmetry=lab)
+        rte_ransac, rre_ransac = eval_pose(T_r, np.eye(4), x[5], axis_symmetry=lab)
+        out.append(dict(symmetry_label=lab, T_est_sym=T_sym, chamfer_dist_sym=ch_sym, T_est_ransac=T_r,
+                        chamfer_dist_ransac=ch_r, sym_success=ok, rte_sym=rte_sym, rre_sym=rre_sym,
+                        rte_ransac=rte_ransac, rre_ransac=rre_ransac))
+    return out
