@@ -54,6 +54,8 @@ SIGNATURES = {
                                c_void_p]),
     "cb_chamfer": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
                            c_void_p, c_void_p]),
+    "cb_chamfer_static": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                                  ctypes.c_char_p, c_size_t, c_void_p]),  # no context argument
     "cb_chamfer_matrix": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cb_chamfer_matrix_half": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cb_self_hausdorff": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),

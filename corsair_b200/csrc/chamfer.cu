@@ -10,6 +10,9 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdarg.h>
+
+#include <mutex>
 
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 ch_pk2(float lo, float hi) {
@@ -264,4 +267,154 @@ extern "C" int cb_chamfer_cross(cb_ctx* ctx, const float* a, int la, int pa, con
                 return rc;
         }
     return CB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// cb_chamfer_static: cb_chamfer for callers that are not allowed to allocate device memory.
+//
+// Everything above takes its scratch (packed float4 copies of both clouds, the per-point
+// (distance, index) keys, the per-block partial sums) from a cb_ctx arena, and cb_create / cb_reserve
+// obtain that arena with cudaMalloc.  Some hosts of this library cannot do that: a plugin running
+// inside an application that has handed all of its device memory to its own pool up front (a
+// PyTorch / TensorRT-style caching allocator set to grab the card, an inference server with a fixed
+// memory budget per model), a real-time loop where cudaMalloc's implicit device synchronisation and
+// unbounded latency are forbidden, or a process whose memory accounting forbids allocations it did
+// not make itself.  For those callers the scratch lives in the module image instead: one file-scope
+// __device__ array of fixed size that every GPU holds from the moment it loads this library until the
+// process exits.  The price is the hard size limit below and that all calls share the one array.
+//
+// The array's name below is only a handle on the host side; the real per-device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current (static_scratch_for).
+constexpr int kStaticMaxPoints = CB_CHAMFER_STATIC_MAX_POINTS;           // per cloud
+constexpr size_t kStaticPartials = (kStaticMaxPoints + 255) / 256;       // blocks of nn3_finalize_kernel
+constexpr size_t kStaticOffA4 = 0;                                        // float4 [max]
+constexpr size_t kStaticOffB4 = kStaticOffA4 + sizeof(float4) * kStaticMaxPoints;
+constexpr size_t kStaticOffBestA = kStaticOffB4 + sizeof(float4) * kStaticMaxPoints;   // u64 [max]
+constexpr size_t kStaticOffBestB = kStaticOffBestA + 8 * (size_t)kStaticMaxPoints;
+constexpr size_t kStaticOffPart = kStaticOffBestB + 8 * (size_t)kStaticMaxPoints;      // 4 x double [partials]
+constexpr size_t kStaticScratchBytes = kStaticOffPart + 4 * 8 * kStaticPartials;
+static_assert(kStaticOffB4 % 256 == 0 && kStaticOffBestA % 256 == 0 && kStaticOffBestB % 256 == 0 &&
+              kStaticOffPart % 256 == 0 && (8 * kStaticPartials) % 256 == 0, "scratch carve-up must stay 256-byte aligned");
+static_assert(kStaticScratchBytes == CB_CHAMFER_STATIC_SCRATCH_BYTES, "header and kernel file disagree on the scratch size");
+
+static __device__ __align__(256) unsigned char g_chamfer_static_scratch[kStaticScratchBytes];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+struct StaticDevice {
+    unsigned char* base = nullptr;  // device address of g_chamfer_static_scratch on this GPU
+    int sm_count = 0;
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mutex;
+
+void static_err(char* h_err, size_t h_err_len, const char* fmt, ...) __attribute__((format(printf, 3, 4)));
+void static_err(char* h_err, size_t h_err_len, const char* fmt, ...) {
+    if (!h_err || h_err_len == 0) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(h_err, h_err_len, fmt, ap);
+    va_end(ap);
+}
+
+// First call on a device: resolve the array's address there and read the SM count.  Neither call
+// allocates on behalf of the caller, but resolving a symbol may make the driver load this module's
+// image, which is why the first call per device belongs outside any stream capture.
+int static_scratch_for(int device, StaticDevice* out, char* h_err, size_t h_err_len) {
+    if (device < 0 || device >= kStaticMaxDevices) {
+        static_err(h_err, h_err_len, "cb_chamfer_static: device ordinal %d outside [0, %d)", device, kStaticMaxDevices);
+        return CB_EUNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticDevice& sd = g_static_dev[device];
+    if (!sd.base) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_chamfer_static_scratch);
+        if (e != cudaSuccess || !p) {
+            static_err(h_err, h_err_len, "cb_chamfer_static: cudaGetSymbolAddress on device %d failed: %s", device,
+                       cudaGetErrorString(e));
+            return CB_ECUDA;
+        }
+        int sms = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess || sms <= 0) {
+            static_err(h_err, h_err_len, "cb_chamfer_static: SM count of device %d unavailable: %s", device,
+                       cudaGetErrorString(e));
+            return CB_ECUDA;
+        }
+        sd.sm_count = sms;
+        sd.base = static_cast<unsigned char*>(p);
+    }
+    *out = sd;
+    return CB_OK;
+}
+
+#define CB_STATIC_CUDA(expr)                                                                          \
+    do {                                                                                              \
+        cudaError_t e_ = (expr);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            static_err(h_err, h_err_len, "cb_chamfer_static: %s failed: %s", #expr, cudaGetErrorString(e_)); \
+            return CB_ECUDA;                                                                          \
+        }                                                                                             \
+    } while (0)
+
+// one search direction with caller-provided scratch; the launch geometry is nn3_direction's, so the
+// (distance, index) keys and the order of every float64 sum are the arena path's
+int static_direction(const StaticDevice& sd, const float* p, int np, const double* Tp, const float4* p4, const float* q,
+                     int nq, const double* Tq, const float4* q4, unsigned long long* best, double* ps, double* pm,
+                     int mode, double* out, int32_t* nn_idx, cudaStream_t st, char* h_err, size_t h_err_len) {
+    // the keys are folded with atomicMin and the array still holds the previous call's: reset them
+    CB_STATIC_CUDA(cudaMemsetAsync(best, 0xff, (size_t)np * 8, st));
+    const int nblk = cb_div_up(np, 256);
+    const int nblk_nn = cb_div_up(np, kNnThreads * kNnPerThread);
+    int S = cb_div_up(4 * sd.sm_count, nblk_nn);
+    S = max(1, min(S, cb_div_up(nq, 256)));
+    const int chunk = cb_div_up(cb_div_up(nq, S), 256) * 256;
+    S = cb_div_up(nq, chunk);
+    nn3_kernel<<<dim3(nblk_nn, S), kNnThreads, 0, st>>>(p4, np, q4, nq, chunk, best);
+    CB_STATIC_CUDA(cudaGetLastError());
+    nn3_finalize_kernel<<<nblk, 256, 0, st>>>(p, np, Tp, q, Tq, best, ps, pm, nn_idx);
+    CB_STATIC_CUDA(cudaGetLastError());
+    nn3_reduce_kernel<<<1, 32, 0, st>>>(ps, pm, nblk, np, mode, out);
+    CB_STATIC_CUDA(cudaGetLastError());
+    return CB_OK;
+}
+}  // namespace
+
+extern "C" int cb_chamfer_static(const float* a, int na, const float* b, int nb, const double* T, int two_dir,
+                                 double* out, int32_t* nn_idx, char* h_err, size_t h_err_len, void* stream) {
+    if (h_err && h_err_len) h_err[0] = 0;
+    if (!a || !b || !out || na <= 0 || nb <= 0) {
+        static_err(h_err, h_err_len, "cb_chamfer_static: empty cloud or null pointer");
+        return CB_EINVAL;
+    }
+    if (na > kStaticMaxPoints || nb > kStaticMaxPoints) {
+        static_err(h_err, h_err_len,
+                   "cb_chamfer_static: clouds of %d and %d points exceed the built-in scratch (at most %d points per "
+                   "cloud); use cb_chamfer with a cb_ctx for larger clouds",
+                   na, nb, kStaticMaxPoints);
+        return CB_EUNSUPPORTED;
+    }
+    int device = -1;
+    CB_STATIC_CUDA(cudaGetDevice(&device));
+    StaticDevice sd;
+    int rc = static_scratch_for(device, &sd, h_err, h_err_len);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float4* a4 = reinterpret_cast<float4*>(sd.base + kStaticOffA4);
+    float4* b4 = reinterpret_cast<float4*>(sd.base + kStaticOffB4);
+    unsigned long long* best_a = reinterpret_cast<unsigned long long*>(sd.base + kStaticOffBestA);
+    unsigned long long* best_b = reinterpret_cast<unsigned long long*>(sd.base + kStaticOffBestB);
+    double* part = reinterpret_cast<double*>(sd.base + kStaticOffPart);
+    pack_points_dev_pose_kernel<<<cb_div_up(na, 256), 256, 0, st>>>(a, na, T, a4);
+    CB_STATIC_CUDA(cudaGetLastError());
+    pack_points_dev_pose_kernel<<<cb_div_up(nb, 256), 256, 0, st>>>(b, nb, nullptr, b4);
+    CB_STATIC_CUDA(cudaGetLastError());
+    rc = static_direction(sd, a, na, T, a4, b, nb, nullptr, b4, best_a, part, part + kStaticPartials, 0, out, nn_idx, st,
+                          h_err, h_err_len);
+    if (rc) return rc;
+    if (two_dir)
+        rc = static_direction(sd, b, nb, nullptr, b4, a, na, T, a4, best_b, part + 2 * kStaticPartials,
+                              part + 3 * kStaticPartials, 1, out, nullptr, st, h_err, h_err_len);
+    return rc;
 }

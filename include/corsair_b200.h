@@ -177,6 +177,32 @@ int cb_fit_minimal(cb_ctx* ctx, const float* src_xyz, const float* tgt_xyz, int 
 int cb_chamfer(cb_ctx* ctx, const float* a, int na, const float* b, int nb, const double* T,
                int two_dir, double* out, int32_t* nn_idx, void* stream);
 
+/* ---- Chamfer without any device allocation ------------------------------------------------------
+ * No counterpart in the reference: this entry point exists for the hosts of this library, not for
+ * the algorithm.  It computes exactly what cb_chamfer computes (same kernels, same launch geometry,
+ * same results) but takes no cb_ctx, because a cb_ctx owns a cudaMalloc'ed arena.  It is meant for
+ * callers that may not allocate device memory themselves: plugins inside an application whose own
+ * pool has already claimed the card (caching allocators, inference servers with a fixed per-model
+ * budget), real-time loops that cannot afford cudaMalloc's device-wide synchronisation, processes
+ * whose memory accounting must see every allocation.  Its scratch is a fixed array in the library's
+ * device image, CB_CHAMFER_STATIC_SCRATCH_BYTES (about 3 MB) on every GPU that loads the library,
+ * held until the process exits.
+ *   - limit: na, nb <= CB_CHAMFER_STATIC_MAX_POINTS each; larger clouds are refused with
+ *     CB_EUNSUPPORTED (use cb_chamfer).  No cudaMalloc / cudaFree / allocating library call is made.
+ *   - device: the CURRENT device of the calling thread (cudaSetDevice), which must own a, b, T, out.
+ *   - the first call on each device looks up the array's address there (cudaGetSymbolAddress) and
+ *     the SM count; make that first call outside any stream capture.  Later calls only launch.
+ *   - every call on a device uses the same array and finds the previous call's contents in it; the
+ *     entry point resets what it needs, but two calls that can run on the GPU at the same time
+ *     (different streams without an ordering between them, or two host threads) corrupt each other.
+ *     Order them on one stream or with events.
+ * a, b, T, two_dir, out, nn_idx, stream as for cb_chamfer.  h_err (HOST, may be NULL) receives the
+ * error text of a failing call, truncated to h_err_len bytes (there is no ctx for cb_last_error). */
+#define CB_CHAMFER_STATIC_MAX_POINTS 65536
+#define CB_CHAMFER_STATIC_SCRATCH_BYTES 3153920
+int cb_chamfer_static(const float* a, int na, const float* b, int nb, const double* T, int two_dir,
+                      double* out, int32_t* nn_idx, char* h_err, size_t h_err_len, void* stream);
+
 /* All-pairs two-direction Chamfer rows of compute_dist (utils/pc_dist.py:61-99):
  * pts [L,P,3] float32; out [(row1-row0), L] float64 rows row0..row1-1 of the full symmetric
  * table; the diagonal is 200 (eye*100 doubled by `table += table.T`, :66,:98). */
