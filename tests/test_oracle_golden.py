@@ -15,6 +15,14 @@ def load(name):
     return np.load(os.path.join(G, name + ".npz"), allow_pickle=False)
 
 
+def f32_close(x, y):
+    """float32 results of torch's CPU broadcast-and-sum (the reference's pdist) agree with the golden
+    file to the last bits only on the host the file was made on: the reduction order over D follows
+    the vector width of the CPU (AVX2 / AVX-512 hosts differ by 1 ulp in a few entries).  Indices are
+    still compared exactly; values within 4 ulp of float32."""
+    return np.allclose(x, y, rtol=4 * np.finfo(np.float32).eps, atol=0)
+
+
 @pytest.mark.parametrize("d", [16, 32])
 def test_find_nn(d):
     g = load("find_nn")
@@ -26,10 +34,10 @@ def test_find_nn(d):
     assert np.array_equal(port.find_nn_cpu(F0, F1), g[f"nn_cpu_idx_{d}"])
     t0, t1 = torch.from_numpy(F0), torch.from_numpy(F1)
     gi, gd = port.find_knn_gpu(t0, t1, 5, nn_max_n=300, return_distance=True)
-    assert np.array_equal(gi.numpy(), g[f"knn_gpu_idx_{d}"]) and np.array_equal(gd.numpy(), g[f"knn_gpu_dist_{d}"])
+    assert np.array_equal(gi.numpy(), g[f"knn_gpu_idx_{d}"]) and f32_close(gd.numpy(), g[f"knn_gpu_dist_{d}"])
     ni, nd = port.find_nn_gpu(t0, t1, nn_max_n=300, return_distance=True, dist_type="L2")
-    assert np.array_equal(ni.numpy(), g[f"nn_gpu_idx_{d}"]) and np.array_equal(nd.numpy(), g[f"nn_gpu_dist_{d}"])
-    assert np.array_equal(port.pdist(t0[:50], t1[:60], "L2").numpy(), g[f"pdist_L2_{d}"])
+    assert np.array_equal(ni.numpy(), g[f"nn_gpu_idx_{d}"]) and f32_close(nd.numpy(), g[f"nn_gpu_dist_{d}"])
+    assert f32_close(port.pdist(t0[:50], t1[:60], "L2").numpy(), g[f"pdist_L2_{d}"])
     # the fp32 broadcast top-k of find_knn_gpu and the float64 KD-tree agree on these inputs
     assert np.array_equal(g[f"knn_gpu_idx_{d}"].reshape(-1, 5), g[f"knn_cpu_idx_{d}"])
     with pytest.raises(NotImplementedError):
