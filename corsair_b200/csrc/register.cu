@@ -506,7 +506,15 @@ extern "C" int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs,
     if (n_jobs < 0 || (n_jobs > 0 && !jobs)) CB_FAIL(ctx, CB_EINVAL, "cb_sym_pose_many: bad arguments");
     CB_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
-    for (int i = 0; i < n_jobs && h_status; ++i) h_status[i] = CB_OK;
+    // a pair that never starts (an earlier one failed) keeps CB_ENOTRUN and gets a recognisable h_out
+    for (int i = 0; i < n_jobs && h_status; ++i) h_status[i] = CB_ENOTRUN;
+    auto mark_not_run = [&](int from) {
+        for (int i = from; i < n_jobs; ++i)
+            if (jobs[i].h_out) {
+                for (int t = 0; t < 40; ++t) jobs[i].h_out[t] = 0.0;
+                jobs[i].h_out[34] = -1.0;
+            }
+    };
     if (n_jobs == 0) return CB_OK;
     if (ctx->timing || concurrency <= 1) {
         // per-class event timing needs one stream: one pair after the other on the caller's
@@ -515,11 +523,14 @@ extern "C" int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs,
             j.in = jobs[i];
             const int rc = sym_run_blocking(ctx, st, j);
             if (h_status) h_status[i] = rc;
-            if (rc) return rc;
+            if (rc) {
+                mark_not_run(i + 1);
+                return rc;
+            }
         }
         return CB_OK;
     }
-    const int W = concurrency < n_jobs ? (concurrency > 32 ? 32 : concurrency) : n_jobs;
+    const int W = std::min(std::min(concurrency, 32), n_jobs);  // every slot owns an arena, staging and streams
     while ((int)ctx->slots.size() < W) {
         cb_ctx* c = nullptr;
         cudaStream_t s = nullptr;
@@ -561,7 +572,11 @@ extern "C" int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs,
             cudaStream_t s = ctx->slot_stream[w];
             if (state[w] == 0) {
                 if (next >= n_jobs || first_rc != CB_OK) {
-                    if (first_rc != CB_OK && next < n_jobs) { done += n_jobs - next; next = n_jobs; }
+                    if (first_rc != CB_OK && next < n_jobs) {
+                        mark_not_run(next);
+                        done += n_jobs - next;
+                        next = n_jobs;
+                    }
                     continue;
                 }
                 which[w] = next++;
@@ -588,6 +603,7 @@ extern "C" int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs,
                     state[w] = 2;
                 } else {
                     sym_finish(job[w]);
+                    if (h_status) h_status[which[w]] = CB_OK;
                     state[w] = 0;
                     ++done;
                 }

@@ -34,7 +34,8 @@ enum cb_status {
     CB_ECUDA = -2,        /* CUDA runtime error (message holds cudaGetErrorString) */
     CB_ENOMEM = -3,       /* workspace allocation failed */
     CB_EUNSUPPORTED = -4, /* valid request the kernels do not cover (e.g. feature width) */
-    CB_ENCCL = -5
+    CB_ENCCL = -5,
+    CB_ENOTRUN = -6       /* cb_sym_pose_many: the pair was never started because an earlier one failed */
 };
 
 /* metric selectors */
@@ -348,8 +349,10 @@ typedef struct cb_sym_job {
  * event of the previous one has completed and never sleeps in the driver while another pair has work
  * to enqueue.  The inputs must be complete on `stream`; on return every h_out is on the host.
  * Results are those of n_jobs cb_sym_pose calls.  h_status [n_jobs] (may be NULL) receives each
- * pair's status; the first failure stops new pairs from starting and is returned.  concurrency <= 1
- * (or timing enabled) runs the pairs one after the other on `stream`. */
+ * pair's status; the first failure stops new pairs from starting and is returned: the pairs that
+ * never started get h_status CB_ENOTRUN and an all-zero h_out with h_out[34] = -1.  At most 32 pairs
+ * are in flight whatever `concurrency` says.  concurrency <= 1 (or timing enabled) runs the pairs one
+ * after the other on `stream`. */
 int cb_sym_pose_many(cb_ctx* ctx, const cb_sym_job* jobs, int n_jobs, int concurrency, int32_t* h_status,
                      void* stream);
 

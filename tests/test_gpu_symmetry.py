@@ -236,6 +236,40 @@ def test_sym_pose_many_reports_a_failing_pair(ctx):
         symmetry.sym_pose_many([bad, bad], workers=2)
 
 
+@pytest.mark.parametrize("concurrency", [1, 2])
+def test_sym_pose_many_status_tells_ok_from_never_run(ctx, concurrency):
+    """h_status of cb_sym_pose_many: 0 for a pair that finished, the error of the pair that failed and
+    CB_ENOTRUN (-6) for every pair that was never started because of it, whose h_out is all zero with
+    h_out[34] = -1 (round-2 advice: 'ok' and 'never ran' must not look alike)."""
+    import ctypes
+    from corsair_b200 import _capi, symmetry, synth
+    p = synth.make_pair(11, 32, "chair", n_raw=2000)
+    good = ((p["baseF"], p["xyz0"], p["posF"], p["xyz1"], 1), dict(k_nn=5, rng=1, n_hypotheses=5000))
+    bad = ((p["baseF"], p["xyz0"], p["posF"][:3], p["xyz1"][:3], 1), dict(k_nn=3, rng=1))  # k_nn 5 > 3 points is caught earlier
+    keep, outs = [], []
+    order = [good, bad, good, good, good, good]
+    recs = (_capi.SymJob * len(order))()
+    for i, (a, k) in enumerate(order):
+        recs[i], out, _ = symmetry._job_record(ctx, a, k, lambda x: ctx.dev(x, torch.float32), keep)
+        out[:] = 123.0
+        outs.append(out)
+    recs[1].k_nn = 5  # more neighbours than target points: the C call rejects this pair
+    status = (ctypes.c_int32 * len(order))(*([77] * len(order)))
+    rc = ctx.lib.cb_sym_pose_many(ctx.handle, ctypes.cast(recs, _capi.c_void_p), len(order), concurrency,
+                                  ctypes.cast(status, _capi.c_void_p), ctx.stream)
+    status = list(status)
+    assert rc < 0 and rc != -6 and status[1] == rc, (rc, status)
+    assert status[0] == 0 and outs[0][34] in (0.0, 1.0, 2.0, 3.0) and outs[0][16] != 123.0
+    assert set(status) <= {0, rc, -6} and status.count(rc) == 1 and -6 in status, status
+    for st, out in zip(status, outs):
+        if st == -6:
+            assert out[34] == -1.0 and not out[:34].any() and not out[35:].any()
+        elif st == 0:
+            assert out[34] >= 0.0 and np.isfinite(out[:34]).all()
+    if concurrency == 1:
+        assert status == [0, rc, -6, -6, -6, -6]
+
+
 @pytest.mark.parametrize("category", ["chair", "table"])
 def test_sym_pose_int_seed_and_streams(ctx, category, monkeypatch):
     """rng=<int> (seed rows replayed in C) equals rng=RandomState(<int>) equals np.random.seed(<int>),
