@@ -569,7 +569,9 @@ int cb_knn_impl(cb_ctx* ctx, const float* q, int nq, const float* r, int nr, int
         if (rc) return rc;
         gamma = knn_cand_tc_gamma(dp);
     } else {
-        if (dp != d) {
+        // the SIMT kernel reads rows as float4: narrower rows and pointers off a 16-byte boundary go through
+        // padded copies in the (aligned) arena
+        if (dp != d || (((size_t)q | (size_t)r) & 15) != 0) {
             float* qpad = cb_alloc_t<float>(ctx, (size_t)nq * dp);
             float* rpad = cb_alloc_t<float>(ctx, (size_t)nr * dp);
             if (!qpad || !rpad) return CB_ENOMEM;

@@ -79,7 +79,7 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 template <int D>
 __global__ void __launch_bounds__(128)
 knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float* __restrict__ r, int nr, int nr_pad,
-                   int d, int maxdot, unsigned perm_a, __nv_bfloat16* __restrict__ Apack,
+                   int d, int vec4, int maxdot, unsigned perm_a, __nv_bfloat16* __restrict__ Apack,
                    __nv_bfloat16* __restrict__ Bpack, int32_t* __restrict__ unscramble,
                    unsigned int* __restrict__ rmax_bits) {
     constexpr int KP = kprime(D);
@@ -101,7 +101,7 @@ knn_tc_pack_kernel(const float* __restrict__ q, int nq, int nq_pad, const float*
             norm = fmaf(b, b, norm);
         };
         if (row < n) {
-            if (d == D) {
+            if (vec4) {  // d == D and both arrays 16-byte aligned (the caller's pointers carry no such promise)
 #pragma unroll
                 for (int c = 0; c < D; c += 4) {
                     const float4 v = *reinterpret_cast<const float4*>(x + c);
@@ -427,10 +427,11 @@ int knn_cand_tc_launch(cb_ctx* ctx, const float* q, int nq, const float* r, int 
         if (g0 == 1) { perm_a %= (unsigned)nr_pad; break; }
     }
     const unsigned pack_blocks = (unsigned)cb_div_up(nq_pad + nr_pad, 128);
+    const int vec4 = d == dp && (((size_t)q | (size_t)r) & 15) == 0;
     if (dp == 16)
-        knn_tc_pack_kernel<16><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, unscramble, rmax_bits);
+        knn_tc_pack_kernel<16><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, vec4, maxdot, perm_a, A, B, unscramble, rmax_bits);
     else
-        knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, maxdot, perm_a, A, B, unscramble, rmax_bits);
+        knn_tc_pack_kernel<32><<<pack_blocks, 128, 0, st>>>(q, nq, nq_pad, r, nr, nr_pad, d, vec4, maxdot, perm_a, A, B, unscramble, rmax_bits);
     CB_LAUNCH_CHECK(ctx);
     cudaError_t e;
     if (dp == 16 && KC == 8) e = launch_tc<16, 8>(A, B, nq, nr, chunk, S, maxdot, nr_pad, cand_idx, bound, st);
