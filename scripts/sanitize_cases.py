@@ -27,6 +27,17 @@ def main():
         ref_idx, ref_d2 = port.find_knn_exact(F0, F1, k)
         assert np.array_equal(idx.cpu().numpy(), ref_idx), "kNN indices"
         print(f"knn {n0}x{n1} d={d} k={k}: ok, fallback rows {ctx.knn_last_fallback_rows()}")
+    # the shape and call of round 2's driver-side failure: find_nn_gpu(dist_type="L2") = k 1, metric 1
+    F0 = rng.standard_normal((1203, 32)).astype(np.float32)
+    F1 = rng.standard_normal((997, 32)).astype(np.float32)
+    F0 /= np.linalg.norm(F0, axis=1, keepdims=True)
+    F1 /= np.linalg.norm(F1, axis=1, keepdims=True)
+    idx, dist = find_nn.knn_device(F0, F1, 1, metric=1, return_distance=True)
+    ref_idx, ref_d2 = port.find_knn_exact(F0, F1, 1)
+    assert np.array_equal(idx.cpu().numpy(), ref_idx), "kNN indices (L2, k=1)"
+    want = np.sqrt(ref_d2.astype(np.float32) + np.float32(1e-7))
+    assert np.allclose(dist.cpu().numpy(), want, rtol=2e-6, atol=0), "kNN L2 distances (k=1)"
+    print(f"knn 1203x997 d=32 k=1 metric=L2: ok, fallback rows {ctx.knn_last_fallback_rows()}")
     # ---- RANSAC: tensor-core scoring with the in-band queue, fold, adaptive stop
     for (m, h) in ((999, 300), (3001, 700)):
         src = rng.uniform(-1, 1, (m, 3)).astype(np.float32)
