@@ -7,6 +7,8 @@
 #      (B200_PROFILING.md).  On the pool this repo was developed on the tool is closed by the operators
 #      ("runs under it have left GPUs needing a reset"); the log then says so and steps 1-2 are the record.
 tool=${1:-memcheck}
+# the debug library is built here, not by __graft_entry__.build() (it doubles the nvcc time of every build)
+make -C corsair_b200/csrc -j8 -s debug || exit 1
 python scripts/sanitize_cases.py > gpurun_out/sanitize_plain.log 2>&1 || { tail -20 gpurun_out/sanitize_plain.log; exit 1; }
 CORSAIR_B200_LIB=$PWD/corsair_b200/lib/libcorsair_b200_dbg.so python scripts/sanitize_cases.py > gpurun_out/sanitize_debuglib.log 2>&1
 echo "debug library exit code $?" >> gpurun_out/sanitize_debuglib.log
