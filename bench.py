@@ -175,18 +175,29 @@ def cpu_pair(q, cad):
                                   seed=SEED, registration=reg)
 
 
-def cpu_sample(sweep, step_index, rng, n_pairs):
-    """Retrieval of the whole step (cdist + stable argsort, utils/retrieval.py:170-177) and n_pairs of
-    its 100 pairs drawn uniformly without replacement."""
+def cpu_sample(sweep, step_index, rng, n_pairs, deadline=None, seconds=None):
+    """Retrieval of the whole step (cdist + stable argsort, utils/retrieval.py:170-177) and up to n_pairs
+    of its 100 pairs drawn uniformly without replacement (at least one; it stops drawing once
+    time.perf_counter() passes `deadline`).  Appends each pair's wall seconds to `seconds`."""
     from scipy.spatial.distance import cdist
     step = sweep.steps[step_index % len(sweep.steps)]
     order = np.argsort(cdist(step["desc"], sweep.lib), axis=1, kind="stable")[:, :TOPK]
     pairs = candidate_pairs(order, step)
     chosen = rng.choice(len(pairs), n_pairs, replace=False)
+    ran = []
     for i in chosen:
+        if ran and deadline is not None and time.perf_counter() > deadline:
+            break
         qi, ci = pairs[int(i)]
+        t = time.perf_counter()
         cpu_pair(step["queries"][qi], sweep.cads[ci])
-    return [int(i) % TOPK for i in chosen]
+        if seconds is not None:
+            seconds.append(time.perf_counter() - t)
+        ran.append(int(i) % TOPK)
+    return ran
+
+
+REF_MIN_PAIRS, REF_MIN_SECONDS = 48, 60.0
 
 
 def run_reference(args, rank, world):
@@ -198,22 +209,26 @@ def run_reference(args, rank, world):
     rng = np.random.default_rng(SEED)  # same draw sequence as the cpu_baseline leg of the GPU arm
     for i in range(args.warmup):
         cpu_sample(sweep, i, rng, 1)
+    # the sample: pairs spread evenly over the K steps until 48 pairs or 60 s, whichever comes first
+    per_step = -(-REF_MIN_PAIRS // max(1, args.steps))
     t0 = time.perf_counter()
-    ranks_drawn = []
+    ranks_drawn, secs = [], []
     for i in range(args.steps):
-        ranks_drawn += cpu_sample(sweep, args.warmup + i, rng, 1)
+        ranks_drawn += cpu_sample(sweep, args.warmup + i, rng, per_step, deadline=t0 + REF_MIN_SECONDS, seconds=secs)
     dt = time.perf_counter() - t0
-    pairs = args.steps
+    pairs = len(ranks_drawn)
     v = pairs / dt
     cores = os.cpu_count()
-    sample = (f"{pairs} pairs: per step one pair drawn uniformly (seed {SEED}) from the step's {PAIRS_PER_STEP} "
-              f"(query, top-10 candidate) pairs, after the step's retrieval; candidate ranks drawn: {ranks_drawn}; "
-              f"OpenMP threads {ransac_c.num_threads()}")
+    sample = (f"{pairs} pairs over {args.steps} steps: after each step's retrieval up to {per_step} of its "
+              f"{PAIRS_PER_STEP} (query, top-10 candidate) pairs drawn uniformly (seed {SEED}), until {REF_MIN_PAIRS} "
+              f"pairs or {REF_MIN_SECONDS:.0f} s; candidate ranks drawn: {ranks_drawn}; OpenMP threads {ransac_c.num_threads()}")
     print(json.dumps({
         "impl": "reference", "metric": "query-CAD pairs registered/sec", "value": v, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": dict(base_config(args, sweep), sample=sample),
+        "config": base_config(args, sweep),
+        "run": {"sample": sample, "pairs_timed": pairs,
+                "seconds_per_pair": {"min": min(secs), "median": float(np.median(secs)), "max": max(secs)}},
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -407,12 +422,13 @@ def run_ours(args, rank, world, local_rank):
         rng = np.random.default_rng(SEED)
         cpu_sample(sweep, 0, rng, 1)  # warm the KD-tree / BLAS / OpenMP pools
         t0 = time.perf_counter()
-        n, drawn = 0, []
+        n, drawn, secs = 0, [], []
         while n < 3 or (time.perf_counter() - t0 < 15 and n < 8):
-            drawn += cpu_sample(sweep, 1 + n, rng, 1)
+            drawn += cpu_sample(sweep, 1 + n, rng, 1, seconds=secs)
             n += 1
         dt = time.perf_counter() - t0
         cpu_base = {"value": n / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                    "seconds_per_pair": {"min": min(secs), "median": float(np.median(secs)), "max": max(secs)},
                     "sample": f"{n} pairs of the same sweep, one drawn uniformly (seed {SEED}) from each of {n} steps' "
                               f"{PAIRS_PER_STEP} pairs after that step's retrieval; candidate ranks drawn {drawn}; "
                               f"OpenMP threads {ransac_c.num_threads()}"}
@@ -422,10 +438,10 @@ def run_ours(args, rank, world, local_rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 search / f64 re-rank, fit and in-band scoring",
         "data": "synthetic",
-        "config": dict(base_config(args, sweep), **{
-            "pairs_timed": pairs, "l2": "256 MiB flush between timed steps", "driver": symmetry.driver_name(),
-            "concurrency": workers, "sequential_ms_per_pair": ms_seq_pair,
-            "sharding": f"queries sharded over {world} rank(s), no data-path collective"}),
+        "config": base_config(args, sweep),  # the same object in both arms; what is specific to this arm is in "run"
+        "run": {"pairs_timed": pairs, "l2": "256 MiB flush between timed steps", "driver": symmetry.driver_name(),
+                "concurrency": workers, "sequential_ms_per_pair": ms_seq_pair,
+                "sharding": f"queries sharded over {world} rank(s), no data-path collective"},
         "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d_step,
                 "d2h_bytes_per_step": d2h_step, "bytes": "counted where the copies are made (Context.dev / Context.host / "
                                                            "the library's own staging), averaged over warm-up + timed steps"},
@@ -465,12 +481,12 @@ def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, m
         ok = bool((torch.gather(d2, 1, idx[rows]) <= torch.topk(d2, K_NN, largest=False).values * (1 + 1e-9) + 1e-12).all())
         tf = 2.0 * 50000 * 10000 * d / (us * 1e-6) / 1e12
         knn_t[f"d{d}"] = {"shape": f"50000 x 10000, D = {d}, k = {K_NN}", "achieved": tf, "unit": "TFLOP/s",
-                          "peak": peaks["bf16_sustained"] / 3.0, "frac": tf / (peaks["bf16_sustained"] / 3.0), "us_per_call": us,
+                          "peak": peaks["bf16_burst"] / 3.0, "frac": tf / (peaks["bf16_burst"] / 3.0), "us_per_call": us,
                           "fallback_rows": fb_rows, "checked_rows_ok": ok}
         del fa, fb, d2
     out["knn_tensor"] = dict(knn_t["d32"], d16=knn_t["d16"],
                              note="whole cb_knn call (packing, tcgen05 candidate kernel, exact re-rank), 2*N0*N1*D flop; "
-                                  f"peak = {peaks['src']} sustained bf16 dense / 3 products")
+                                  f"peak = {peaks['src']} BURST bf16 dense / 3 products (ten calls timed alone, ~2 ms)")
 
     # ---- C5: table category, pos_sym from the real histogram, 50k-point scans, 4096 hypotheses
     labels = np.repeat(list(TABLE_SYM_HIST), list(TABLE_SYM_HIST.values()))
@@ -561,7 +577,8 @@ def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, m
     stack_d = torch.from_numpy(stack.astype(np.float32)).to(dev)
     barrier()
     t0 = time.perf_counter()
-    table = cdist_mod.chamfer_matrix_sharded(stack_d)
+    c4_phases = {}
+    table = cdist_mod.chamfer_matrix_sharded(stack_d, timings=c4_phases)
     barrier()
     sec = max_over_ranks(time.perf_counter() - t0)
     rows = [0, 1, C4_L // 2, C4_L - 1]
@@ -571,15 +588,17 @@ def side_workloads(args, rank, world, dev, dist, ctx, peaks, workers, barrier, m
         ref_rows[k_, r] = got[k_, r]  # the diagonal convention (200) is the table's
     n_pairs = C4_L * (C4_L - 1) // 2
     evals = n_pairs * float(C4_P) * C4_P  # one distance tile feeds both directions
-    fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12
+    fp32_peak = 67.1  # measured: scripts/microbench/fp64_rate.cu, profiles/r02_fp64_rate.txt (nominal 74.4)
     out["c4"] = {"value": n_pairs / sec, "unit": "cloud pairs/s", "seconds": sec, "clouds": C4_L, "points": C4_P, "ranks": world,
                  "rows_equal_to_single_gpu": bool(np.array_equal(got, ref_rows)),
                  "symmetric": bool(np.array_equal(table, table.T)), "diagonal": float(table[0, 0]),
                  "roofline": {"bound": "fp32", "achieved": evals * 8 / sec / 1e12 / world, "unit": "TFLOP/s per GPU",
                               "peak": fp32_peak, "frac": evals * 8 / sec / 1e12 / world / fp32_peak,
                               "note": "8 flop per point-pair evaluation (SURVEY 8d), wall time of the whole sharded call incl. the "
-                                      "all-gather, the device->host read of the table and H + H^T; peak = nominal fp32 FMA rate "
-                                      "(148 SMs x 128 lanes x 2 x 1.965 GHz), no measured fp32 peak exists"},
+                                      "all-gather, H + H^T on the device and the device->host read of the table (split in "
+                                      "`phases_s`, this rank's wall seconds); peak = the fp32 FMA rate this repo measured on a "
+                                      "B200 (profiles/r02_fp64_rate.txt: 67.1 TFLOP/s; nominal 74.4)"},
+                 "phases_s": {k_: round(v_, 4) for k_, v_ in c4_phases.items()},
                  "workload": "C4: all-pairs Chamfer table (utils/pc_dist.py:61-99), row blocks over the ranks, one all-gather"}
     sharded["chamfer_rows_sharded"] = {"seconds": sec, "equal_to_single_gpu": out["c4"]["rows_equal_to_single_gpu"], "ranks": world}
     out["sharded"] = sharded

@@ -139,3 +139,27 @@ def test_compute_dist_clouds_of_different_sizes(ctx, rng, as_numpy):
     assert isinstance(got, np.ndarray) and got.shape == (4, 4)
     np.testing.assert_allclose(got, ref, rtol=1e-5)
     assert np.array_equal(got, got.T) and np.all(np.diag(got) == 200)
+
+
+@pytest.mark.parametrize("L,P", [(7, 100), (5, 2049), (9, 31), (4, 4266), (6, 1)])
+def test_chamfer_table_one_tile_equals_two_sweeps(ctx, rng, L, P, monkeypatch):
+    """The table kernel takes both directions from ONE distance tile (like the reference's single [m, n]
+    matrix with min(0) and min(1), utils/pc_dist.py:45-52: cloud i in registers, cloud j streamed, the
+    streamed points' minima through warp minima and shared-memory atomicMin).  The two-sweep kernel of
+    rounds 1-2 is kept behind CORSAIR_B200_CHAMFER_TWO_SWEEPS=1; both evaluate the same fp32 distances and
+    add them in the same order, so full tables, half tables and row blocks agree bit for bit."""
+    from corsair_b200 import pc_dist
+    pts = rng.standard_normal((L, P, 3)).astype(np.float32)
+    got = {}
+    for two in ("0", "1"):
+        monkeypatch.setenv("CORSAIR_B200_CHAMFER_TWO_SWEEPS", two)
+        got[two] = [pc_dist.chamfer_rows_device(pts).cpu().numpy(),
+                    pc_dist.chamfer_rows_device(pts, half=True).cpu().numpy(),
+                    pc_dist.chamfer_rows_device(pts, 1, 3).cpu().numpy()]
+    for a, b in zip(got["0"], got["1"]):
+        assert np.array_equal(a, b)
+    full = got["0"][0]
+    assert np.array_equal(full, full.T) and np.all(np.diag(full) == 200)
+    # ... and against the pairwise entry point (float64 re-evaluated neighbour distances): 1e-6 relative
+    ref01 = pc_dist.chamfer(pts[0], pts[1]).item()
+    assert abs(full[0, 1] - ref01) <= 1e-6 * ref01
