@@ -108,8 +108,25 @@ __device__ __forceinline__ f32x2 cm_fma2(f32x2 a, f32x2 b, f32x2 c) {
     return r;
 }
 
-constexpr int kCmThreads = 256;
-constexpr int kCmPerThread = 8;  // query points per thread and sweep (four packed pairs)
+// build knobs (measured variants: see DESIGN.md K4b)
+#ifndef CM_THREADS
+#define CM_THREADS 256
+#endif
+#ifndef CM_PER_THREAD
+#define CM_PER_THREAD 8
+#endif
+#ifndef CM_UNROLL
+#define CM_UNROLL 2
+#endif
+#ifndef CM_MINBLOCKS
+#define CM_MINBLOCKS 3
+#endif
+#define CM_STR2(x) #x
+#define CM_STR(x) CM_STR2(x)
+constexpr int kCmThreads = CM_THREADS;
+constexpr int kCmPerThread = CM_PER_THREAD;  // query points per thread and sweep (packed pairs)
+constexpr int kCmWarps = kCmThreads / 32;
+constexpr int kCmUnroll = CM_UNROLL;
 
 // mean over the points of X of the distance to the nearest point of Y; Y sits in shared memory as
 // three arrays of NEGATED, duplicated coordinates (-v, -v) so that one packed add gives p - v for
@@ -233,11 +250,11 @@ __device__ __forceinline__ bool cm_block_role(int i, int j, int L, int row0, int
     return true;
 }
 
-__global__ void __launch_bounds__(kCmThreads, 3)  // 28 P bytes of shared memory: three blocks per SM at P = 2048
+__global__ void __launch_bounds__(kCmThreads, CM_MINBLOCKS)  // 28 P bytes of shared memory: three blocks per SM at P = 2048
 chamfer_matrix_kernel(const float* __restrict__ pts, int L, int P, int row0, int row1, int half,
                       double* __restrict__ out) {
     extern __shared__ float2 cm2_smem[];
-    __shared__ double wsum[2][8];
+    __shared__ double wsum[2][kCmWarps];
     const int i = row0 + blockIdx.y, j = blockIdx.x;
     double* o = out + (size_t)blockIdx.y * L + j;
     bool mirror_here;
@@ -279,7 +296,7 @@ chamfer_matrix_kernel(const float* __restrict__ pts, int L, int P, int row0, int
         for (int ub = 0; ub < P32; ub += 32) {
             // lane l keeps the warp's minimum for streamed point ub + l; one conflict-free atomicMin per 32 points
             unsigned mine = 0x7f800000u;
-#pragma unroll 2
+#pragma unroll kCmUnroll
             for (int t = 0; t < 32; t += 2) {
                 // two streamed points per step: one 16-byte shared-memory read per coordinate, and the register
                 // points' minima take both distances in one three-input minimum
@@ -300,10 +317,15 @@ chamfer_matrix_kernel(const float* __restrict__ pts, int L, int P, int row0, int
                     bd[2 * k + 1] = fminf(fminf(bd[2 * k + 1], d0[2 * k + 1]), d1[2 * k + 1]);
                 }
                 // each streamed point's minimum over this warp's 256 register points
-                const float m0 = fminf(fminf(fminf(d0[0], d0[1]), d0[2]),
-                                       fminf(fminf(fminf(d0[3], d0[4]), d0[5]), fminf(d0[6], d0[7])));
-                const float m1 = fminf(fminf(fminf(d1[0], d1[1]), d1[2]),
-                                       fminf(fminf(fminf(d1[3], d1[4]), d1[5]), fminf(d1[6], d1[7])));
+                float m0 = fminf(fminf(fminf(d0[0], d0[1]), d0[2]),
+                                 fminf(fminf(fminf(d0[3], d0[4]), d0[5]), fminf(d0[6], d0[7])));
+                float m1 = fminf(fminf(fminf(d1[0], d1[1]), d1[2]),
+                                 fminf(fminf(fminf(d1[3], d1[4]), d1[5]), fminf(d1[6], d1[7])));
+#pragma unroll
+                for (int k = 8; k + 1 < kCmPerThread; k += 2) {
+                    m0 = fminf(fminf(m0, d0[k]), d0[k + 1]);
+                    m1 = fminf(fminf(m1, d1[k]), d1[k + 1]);
+                }
                 const unsigned w0 = __reduce_min_sync(0xffffffffu, __float_as_uint(m0));
                 const unsigned w1 = __reduce_min_sync(0xffffffffu, __float_as_uint(m1));
                 mine = lane == t ? w0 : mine;
@@ -334,7 +356,7 @@ chamfer_matrix_kernel(const float* __restrict__ pts, int L, int P, int row0, int
     __syncthreads();
     if (threadIdx.x == 0) {
         double sa = 0.0, sb = 0.0;
-        for (int w = 0; w < 8; ++w) { sa += wsum[0][w]; sb += wsum[1][w]; }
+        for (int w = 0; w < kCmWarps; ++w) { sa += wsum[0][w]; sb += wsum[1][w]; }
         // order the two directional means by cloud index so (i,j) and (j,i) add identically
         const double ma = sa / P, mb = sb / P;
         const double v = i < j ? ma + mb : mb + ma;
